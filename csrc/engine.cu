@@ -1,0 +1,1116 @@
+// Engine: domain decomposition, device arena, multi-process bootstrap, grid load/store and the
+// epoch driver with the reference's exact early-exit semantics.
+//
+// Replaces: MPI_Cart_create / Cart_coords / Cart_rank topology (C:120-137, C:225-275), the
+// generation loops (S:169-203, C:328-370, G:213-297), master scatter/gather (M:221-254,
+// M:429-472), MPI-IO subarray read/write (A:174-201, C:174-198, C:379-445), timers
+// (S:175, M:187.., T:8-20) and the compile-time configuration (S:6-9).
+//
+// Driver design.  Both early exits of the reference are fixed points (an empty grid stays
+// empty; g_e == g_(e-1) implies every later generation is equal), so generations are run
+// speculatively in batches of `batch_gens` without any host round trip: only the last epoch
+// of a batch reduces the alive / changed bits (fused in the generation kernel), a one-CTA
+// gather kernel all-reduces them across domains, and the host looks at one 8-byte word per
+// batch.  When a batch ends dead or unchanged, the batch is replayed from its untouched
+// input buffer one generation at a time with per-generation flags, and the serial loop is
+// evaluated literally on those flags to obtain the exact "Generations:" value.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cerrno>
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
+#include <vector>
+
+#include "gol_internal.h"
+
+namespace {
+
+constexpr int G = GOL_GHOST_ROWS;
+constexpr int kMaxBatch = 512;
+
+struct LocalDomain {
+    int gid = 0, r = 0, c = 0;
+    int64_t x0 = 0, y0 = 0;
+    gol_layout L{};
+    int strips = 0;
+};
+
+// Device arena of one process: every process can compute every other process's arena layout
+// from the configuration alone, so one IPC handle per process is all that has to be exchanged.
+struct ArenaLayout {
+    std::vector<int64_t> buf_off;     // [local domain][GOL_NBUF] byte offsets
+    std::vector<int64_t> flags_off;   // [local domain]
+    std::vector<int64_t> scratch_off; // [local domain]
+    int64_t rec_off = 0;
+    int64_t total = 0;
+};
+
+struct IpcBlob {
+    cudaIpcMemHandle_t handle;
+    int32_t device;
+    int32_t pid;
+    int64_t arena_bytes;
+};
+
+}  // namespace
+
+struct gol_engine {
+    gol_config cfg{};
+    int R = 1, C = 1, ndom = 1, P = 1, rank = 0, per_proc = 1;
+    std::vector<int64_t> col_x, row_y;  // domain boundaries (C+1, R+1)
+    bool fast = false;
+    int num_sms = 148;
+
+    // strip path
+    std::vector<LocalDomain> local;
+    ArenaLayout arena_layout;
+    char *arena = nullptr;
+    std::vector<char *> peer_arena;  // [P]; own entry = arena
+    bool imported = false;
+    GolDomainDev *d_doms = nullptr;
+    unsigned long long **d_rec_tables = nullptr;
+    unsigned long long *d_results = nullptr;  // [kMaxBatch + 1]
+    unsigned long long *h_results = nullptr;  // pinned
+    unsigned int *d_error = nullptr;
+    int max_strips = 1;
+    int64_t max_h = 1;
+
+    // dense path (tiny grids, single domain)
+    uint64_t *dense[3] = {nullptr, nullptr, nullptr};
+    uint32_t *d_dflags = nullptr;  // [kMaxBatch + 1][2]
+    uint32_t *h_dflags = nullptr;  // pinned
+
+    int cur = 0;
+    uint32_t seq = 0, rec_seq = 0;
+    bool prepared = false;
+    int64_t launches = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    double last_ms = 0.0;
+    int kmax = 4, batch = 120;
+};
+
+namespace {
+
+int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
+
+void domain_extent(const gol_engine *e, int gid, int64_t *x0, int64_t *y0, int64_t *w, int64_t *h)
+{
+    const int r = gid / e->C, c = gid % e->C;
+    *x0 = e->col_x[c];
+    *y0 = e->row_y[r];
+    *w = e->col_x[c + 1] - e->col_x[c];
+    *h = e->row_y[r + 1] - e->row_y[r];
+}
+
+int neighbor_gid(const gol_engine *e, int gid, int dir)
+{
+    const int r = gid / e->C, c = gid % e->C;
+    const int nr = (r + GOL_DIR_DY[dir] + e->R) % e->R, nc = (c + GOL_DIR_DX[dir] + e->C) % e->C;
+    return nr * e->C + nc;
+}
+
+int owner_of(const gol_engine *e, int gid) { return gid / e->per_proc; }
+
+// arena layout of process p
+int build_arena_layout(const gol_engine *e, int p, ArenaLayout *A)
+{
+    A->buf_off.assign((size_t)e->per_proc * GOL_NBUF, 0);
+    A->flags_off.assign((size_t)e->per_proc, 0);
+    A->scratch_off.assign((size_t)e->per_proc, 0);
+    int64_t off = 0;
+    for (int i = 0; i < e->per_proc; ++i) {
+        const int gid = p * e->per_proc + i;
+        int64_t x0, y0, w, h;
+        domain_extent(e, gid, &x0, &y0, &w, &h);
+        gol_layout L;
+        GOL_TRY(gol_layout_init(&L, w, h));
+        for (int b = 0; b < GOL_NBUF; ++b) {
+            A->buf_off[(size_t)i * GOL_NBUF + b] = off;
+            off = align_up(off + L.buffer_words32 * 4, 256);
+        }
+    }
+    for (int i = 0; i < e->per_proc; ++i) {
+        A->flags_off[(size_t)i] = off;
+        off += 256;
+        A->scratch_off[(size_t)i] = off;
+        off += 256;
+    }
+    A->rec_off = off;
+    off = align_up(off + (int64_t)GOL_REC_SLOTS * e->ndom * 8, 256);
+    A->total = off;
+    return 0;
+}
+
+// (Re)build the device-side domain descriptors from the local + peer arenas.
+int upload_domains(gol_engine *e)
+{
+    std::vector<GolDomainDev> doms((size_t)e->per_proc);
+    std::vector<ArenaLayout> layouts((size_t)e->P);
+    for (int p = 0; p < e->P; ++p) GOL_TRY(build_arena_layout(e, p, &layouts[(size_t)p]));
+    std::vector<unsigned long long *> tables((size_t)e->P, nullptr);
+    for (int p = 0; p < e->P; ++p)
+        if (e->peer_arena[(size_t)p])
+            tables[(size_t)p] = reinterpret_cast<unsigned long long *>(e->peer_arena[(size_t)p] + layouts[(size_t)p].rec_off);
+    GOL_CUDA(cudaMemcpy(e->d_rec_tables, tables.data(), sizeof(void *) * (size_t)e->P, cudaMemcpyHostToDevice));
+
+    for (int i = 0; i < e->per_proc; ++i) {
+        const LocalDomain &ld = e->local[(size_t)i];
+        GolDomainDev &D = doms[(size_t)i];
+        memset(&D, 0, sizeof D);
+        const ArenaLayout &A = layouts[(size_t)e->rank];
+        for (int b = 0; b < GOL_NBUF; ++b)
+            D.buf[b] = reinterpret_cast<uint32_t *>(e->arena + A.buf_off[(size_t)i * GOL_NBUF + b]);
+        D.H = (int32_t)ld.L.height;
+        D.nw32 = ld.L.nw32;
+        D.nwf32 = 2 * ld.L.nqf;
+        D.rem = ld.L.rem;
+        D.pitch32 = ld.L.pitch32;
+        D.strips = ld.strips;
+        D.global_id = ld.gid;
+        D.epoch_flags = reinterpret_cast<uint32_t *>(e->arena + A.flags_off[(size_t)i]);
+        D.scratch = reinterpret_cast<GolScratch *>(e->arena + A.scratch_off[(size_t)i]);
+        D.rec_tables = e->d_rec_tables;
+        D.proc_count = e->P;
+        D.num_domains = e->ndom;
+        for (int d = 0; d < GOL_NDIR; ++d) {
+            const int ngid = neighbor_gid(e, ld.gid, d);
+            const int q = owner_of(e, ngid), li = ngid - q * e->per_proc;
+            char *base = e->peer_arena[(size_t)q];
+            GolNeighbor &N = D.nb[d];
+            int64_t x0, y0, w, h;
+            domain_extent(e, ngid, &x0, &y0, &w, &h);
+            gol_layout NL;
+            GOL_TRY(gol_layout_init(&NL, w, h));
+            N.H = (int32_t)h;
+            N.nw32 = NL.nw32;
+            N.rem = NL.rem;
+            N.pitch32 = NL.pitch32;
+            if (base) {
+                const ArenaLayout &NA = layouts[(size_t)q];
+                for (int b = 0; b < GOL_NBUF; ++b)
+                    N.buf[b] = reinterpret_cast<uint32_t *>(base + NA.buf_off[(size_t)li * GOL_NBUF + b]);
+                N.flag = reinterpret_cast<uint32_t *>(base + NA.flags_off[(size_t)li]) + GOL_DIR_OPP[d];
+            }
+        }
+    }
+    GOL_CUDA(cudaMemcpy(e->d_doms, doms.data(), sizeof(GolDomainDev) * doms.size(), cudaMemcpyHostToDevice));
+    return 0;
+}
+
+// Launch geometry for temporal depth k: chunk height trades apron redundancy (2k rows per
+// chunk) against the number of independent warps.
+void geometry(const gol_engine *e, int k, GolLaunch *lp)
+{
+    const int64_t target_items = (int64_t)e->num_sms * 16 / std::max(1, e->per_proc);
+    int64_t chunks = std::max<int64_t>(1, (target_items + e->max_strips - 1) / e->max_strips);
+    int64_t rows = gol_div_up(e->max_h, chunks);
+    const int64_t min_rows = std::min<int64_t>(e->max_h, std::max<int64_t>(8, 6 * k));
+    if (rows < min_rows) rows = min_rows;
+    chunks = gol_div_up(e->max_h, rows);
+    lp->chunk_rows = (int32_t)rows;
+    lp->chunks = (int32_t)chunks;
+    lp->ctas_per_domain = (int32_t)gol_div_up(chunks * e->max_strips, 4);
+}
+
+bool multi(const gol_engine *e) { return e->P > 1; }
+
+int check_ready(gol_engine *e, const char *what)
+{
+    if (e->P > 1 && !e->imported) GOL_FAIL("%s: multi-process engine used before gol_engine_ipc_import", what);
+    return 0;
+}
+
+// one strip-kernel epoch: k generations from buffer `in` to buffer `out`
+int launch_epoch(gol_engine *e, int k, int in, int out, bool flags, int rec_slot, uint32_t rec_seq)
+{
+    GolLaunch lp{};
+    geometry(e, k, &lp);
+    lp.in_idx = in;
+    lp.out_idx = out;
+    lp.wait_seq = multi(e) ? e->seq : 0;
+    lp.seq = ++e->seq;
+    lp.signal = multi(e) ? 1 : 0;
+    lp.rec_slot = flags ? rec_slot : -1;
+    lp.rec_seq = rec_seq;
+    GOL_TRY(gol_launch_strip(e->d_doms, e->per_proc, lp, k, flags ? 1 : 0, 0, e->stream));
+    ++e->launches;
+    return 0;
+}
+
+// Run n generations starting from e->cur as epochs of at most kmax; buffers `keep` is never
+// written.  With want_flags the last epoch publishes a record (rec slot/seq returned).
+int run_epochs(gol_engine *e, int64_t n, int keep, bool want_flags, bool per_gen_flags, int kcap)
+{
+    int a = -1, b = -1;
+    for (int i = 0; i < GOL_NBUF && b < 0; ++i) {
+        if (i == keep || i == e->cur) continue;
+        if (a < 0) a = i; else b = i;
+    }
+    int in = e->cur;
+    int64_t left = n;
+    int which = 0;
+    while (left > 0) {
+        int k = 1;
+        if (!per_gen_flags) {
+            const int cap = (int)std::min<int64_t>(left, kcap);
+            while (k * 2 <= cap) k *= 2;
+        }
+        int out = which ? b : a;
+        if (out == in) out = which ? a : b;
+        const bool last = left - k == 0;
+        const bool f = per_gen_flags || (want_flags && last);
+        uint32_t rs = 0;
+        int slot = -1;
+        if (f) {
+            rs = ++e->rec_seq;
+            slot = (int)(rs % GOL_REC_SLOTS);
+        }
+        GOL_TRY(launch_epoch(e, k, in, out, f, slot, rs));
+        if (f && per_gen_flags) {
+            // in replay mode every generation is gathered (also keeps the record ring bounded)
+            const ArenaLayout &A = e->arena_layout;
+            GOL_TRY(gol_launch_gather(reinterpret_cast<unsigned long long *>(e->arena + A.rec_off), slot, e->ndom,
+                                      rs, e->d_results + (n - left), e->d_error, e->stream));
+            ++e->launches;
+        }
+        in = out;
+        which ^= 1;
+        left -= k;
+    }
+    e->cur = in;
+    return 0;
+}
+
+int gather_last(gol_engine *e, int result_index)
+{
+    const uint32_t rs = e->rec_seq;
+    const ArenaLayout &A = e->arena_layout;
+    GOL_TRY(gol_launch_gather(reinterpret_cast<unsigned long long *>(e->arena + A.rec_off),
+                              (int)(rs % GOL_REC_SLOTS), e->ndom, rs, e->d_results + result_index, e->d_error,
+                              e->stream));
+    ++e->launches;
+    return 0;
+}
+
+int fetch_results(gol_engine *e, int count)
+{
+    GOL_CUDA(cudaMemcpyAsync(e->h_results, e->d_results, sizeof(unsigned long long) * (size_t)count,
+                             cudaMemcpyDeviceToHost, e->stream));
+    unsigned int err = 0;
+    GOL_CUDA(cudaMemcpyAsync(&e->h_results[kMaxBatch + 1], e->d_error, sizeof(unsigned int), cudaMemcpyDeviceToHost,
+                             e->stream));
+    GOL_CUDA(cudaStreamSynchronize(e->stream));
+    err = (unsigned int)e->h_results[kMaxBatch + 1];
+    if (err) GOL_FAIL("device-side wait timed out (code %u): a neighbouring rank stopped making progress", err);
+    return 0;
+}
+
+// Literal evaluation of the serial loop (S:177-196) on per-generation flags.
+// alive[i], diff[i] describe generation gen0+i (i = 0..n); generation gen0 is known alive.
+void resolve_exit(int64_t gen0, int n, const std::vector<int> &alive, const std::vector<int> &diff, int limit,
+                  int freq, int *generations, int *reason)
+{
+    for (int i = 1; i <= n; ++i) {
+        const int64_t ord = gen0 + i;  // evolve ordinal
+        if (!alive[(size_t)i - 1]) { *generations = (int)(ord - 1); *reason = GOL_EXIT_EMPTY; return; }
+        if (freq > 0 && ord % freq == 0 && !diff[(size_t)i]) { *generations = (int)(ord - 1); *reason = GOL_EXIT_SIMILAR; return; }
+    }
+    const int64_t end = gen0 + n;
+    if (!alive[(size_t)n]) { *generations = (int)end; *reason = GOL_EXIT_EMPTY; return; }
+    if (freq > 0 && !diff[(size_t)n]) {
+        const int64_t next = (end / freq + 1) * freq;  // next similarity check after `end`
+        if (next <= limit) { *generations = (int)(next - 1); *reason = GOL_EXIT_SIMILAR; return; }
+    }
+    *generations = limit;
+    *reason = GOL_EXIT_LIMIT;
+}
+
+int fill_population(gol_engine *e, gol_result *res)
+{
+    uint64_t pop = 0;
+    GOL_TRY(gol_engine_population(e, &pop));
+    res->population = pop;
+    return 0;
+}
+
+// ------------------------------------------------------------ strip-path run
+int run_fast(gol_engine *e, gol_result *res)
+{
+    const int limit = e->cfg.gen_limit, freq = e->cfg.similarity_frequency;
+    GOL_CUDA(cudaEventRecord(e->ev0, e->stream));
+    // empty() of generation 0
+    {
+        GolLaunch lp{};
+        geometry(e, 1, &lp);
+        lp.in_idx = e->cur;
+        lp.out_idx = e->cur;
+        lp.seq = e->seq;  // no ghost traffic: sequence unchanged
+        lp.signal = 0;
+        const uint32_t rs = ++e->rec_seq;
+        lp.rec_slot = (int)(rs % GOL_REC_SLOTS);
+        lp.rec_seq = rs;
+        GOL_TRY(gol_launch_scan_alive(e->d_doms, e->per_proc, lp, e->stream));
+        ++e->launches;
+        GOL_TRY(gather_last(e, 0));
+        GOL_TRY(fetch_results(e, 1));
+    }
+    int generations = 0, reason = GOL_EXIT_LIMIT;
+    int64_t computed = 0;
+    if (!(e->h_results[0] & 1ull)) {
+        generations = 0;
+        reason = GOL_EXIT_EMPTY;
+    } else {
+        int64_t gen = 0;
+        generations = limit;
+        while (gen < limit) {
+            const int n = (int)std::min<int64_t>(e->batch, limit - gen);
+            const int ckpt = e->cur;
+            GOL_TRY(run_epochs(e, n, ckpt, true, false, e->kmax));
+            GOL_TRY(gather_last(e, 0));
+            GOL_TRY(fetch_results(e, 1));
+            computed += n;
+            const bool alive_end = e->h_results[0] & 1ull, diff_end = e->h_results[0] & 2ull;
+            if (!alive_end || (freq > 0 && !diff_end)) {
+                // replay the batch one generation at a time from its untouched input
+                e->cur = ckpt;
+                GOL_TRY(run_epochs(e, n, ckpt, true, true, 1));
+                GOL_TRY(fetch_results(e, n));
+                computed += n;
+                std::vector<int> alive((size_t)n + 1), diff((size_t)n + 1);
+                alive[0] = 1;
+                diff[0] = 1;
+                for (int i = 1; i <= n; ++i) {
+                    alive[(size_t)i] = (int)(e->h_results[i - 1] & 1ull);
+                    diff[(size_t)i] = (int)((e->h_results[i - 1] >> 1) & 1ull);
+                }
+                resolve_exit(gen, n, alive, diff, limit, freq, &generations, &reason);
+                break;
+            }
+            gen += n;
+        }
+    }
+    GOL_CUDA(cudaEventRecord(e->ev1, e->stream));
+    GOL_CUDA(cudaEventSynchronize(e->ev1));
+    float ms = 0;
+    GOL_CUDA(cudaEventElapsedTime(&ms, e->ev0, e->ev1));
+    e->last_ms = ms;
+    if (res) {
+        memset(res, 0, sizeof *res);
+        res->generations = generations;
+        res->exit_reason = reason;
+        res->generations_computed = computed;
+        res->loop_ms = ms;
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------ dense-path run
+int dense_steps(gol_engine *e, int n, bool flags)
+{
+    const int64_t W = e->cfg.width, H = e->cfg.height;
+    for (int i = 0; i < n; ++i) {
+        const int out = (e->cur + 1) % 3 == 2 ? 0 : (e->cur + 1) % 3;  // ping-pong 0 <-> 1 (2 = checkpoint, unused)
+        GOL_TRY(gol_op_step_dense(e->dense[e->cur], e->dense[out], W, H, flags ? e->d_dflags + 2 * (i + 1) : nullptr,
+                                  e->stream));
+        ++e->launches;
+        e->cur = out;
+    }
+    return 0;
+}
+
+int run_dense(gol_engine *e, gol_result *res)
+{
+    const int limit = e->cfg.gen_limit, freq = e->cfg.similarity_frequency;
+    const int64_t W = e->cfg.width, H = e->cfg.height;
+    GOL_CUDA(cudaEventRecord(e->ev0, e->stream));
+    int generations = limit, reason = GOL_EXIT_LIMIT;
+    int64_t computed = 0, gen = 0;
+    bool known_alive = false;
+    while (gen < limit) {
+        const int n = (int)std::min<int64_t>(std::min(e->batch, kMaxBatch), limit - gen);
+        GOL_CUDA(cudaMemsetAsync(e->d_dflags, 0, sizeof(uint32_t) * 2 * (size_t)(n + 1), e->stream));
+        if (!known_alive) {
+            GOL_TRY(gol_op_flags_dense(e->dense[e->cur], nullptr, W, H, e->d_dflags, e->stream));
+            ++e->launches;
+        }
+        GOL_TRY(dense_steps(e, n, true));
+        GOL_CUDA(cudaMemcpyAsync(e->h_dflags, e->d_dflags, sizeof(uint32_t) * 2 * (size_t)(n + 1),
+                                 cudaMemcpyDeviceToHost, e->stream));
+        GOL_CUDA(cudaStreamSynchronize(e->stream));
+        computed += n;
+        std::vector<int> alive((size_t)n + 1), diff((size_t)n + 1);
+        for (int i = 0; i <= n; ++i) {
+            alive[(size_t)i] = (int)e->h_dflags[2 * i];
+            diff[(size_t)i] = (int)e->h_dflags[2 * i + 1];
+        }
+        if (known_alive) alive[0] = 1;
+        diff[0] = 1;
+        const bool alive_end = alive[(size_t)n], diff_end = diff[(size_t)n];
+        if (!alive[0] || !alive_end || (freq > 0 && !diff_end)) {
+            resolve_exit(gen, n, alive, diff, limit, freq, &generations, &reason);
+            break;
+        }
+        known_alive = true;
+        gen += n;
+    }
+    GOL_CUDA(cudaEventRecord(e->ev1, e->stream));
+    GOL_CUDA(cudaEventSynchronize(e->ev1));
+    float ms = 0;
+    GOL_CUDA(cudaEventElapsedTime(&ms, e->ev0, e->ev1));
+    e->last_ms = ms;
+    if (res) {
+        memset(res, 0, sizeof *res);
+        res->generations = generations;
+        res->exit_reason = reason;
+        res->generations_computed = computed;
+        res->loop_ms = ms;
+    }
+    return 0;
+}
+
+}  // namespace
+
+// =============================================================== C ABI
+extern "C" {
+
+int gol_cuda_available(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n > 0 ? 1 : 0;
+}
+
+void gol_config_default(gol_config *cfg, int64_t width, int64_t height)
+{
+    memset(cfg, 0, sizeof *cfg);
+    cfg->width = width;
+    cfg->height = height;
+    cfg->grid_rows = 1;
+    cfg->grid_cols = 1;
+    cfg->proc_rank = 0;
+    cfg->proc_count = 1;
+    cfg->device = 0;
+    cfg->gen_limit = GOL_DEFAULT_GEN_LIMIT;
+    cfg->similarity_frequency = GOL_DEFAULT_SIMILARITY_FREQUENCY;
+}
+
+void gol_engine_destroy(gol_engine *e)
+{
+    if (!e) return;
+    cudaSetDevice(e->cfg.device);
+    if (e->stream) cudaStreamSynchronize(e->stream);
+    for (int p = 0; p < (int)e->peer_arena.size(); ++p)
+        if (p != e->rank && e->peer_arena[(size_t)p]) cudaIpcCloseMemHandle(e->peer_arena[(size_t)p]);
+    if (e->arena) cudaFree(e->arena);
+    if (e->d_doms) cudaFree(e->d_doms);
+    if (e->d_rec_tables) cudaFree(e->d_rec_tables);
+    if (e->d_results) cudaFree(e->d_results);
+    if (e->h_results) cudaFreeHost(e->h_results);
+    if (e->d_error) cudaFree(e->d_error);
+    for (auto &d : e->dense)
+        if (d) cudaFree(d);
+    if (e->d_dflags) cudaFree(e->d_dflags);
+    if (e->h_dflags) cudaFreeHost(e->h_dflags);
+    if (e->ev0) cudaEventDestroy(e->ev0);
+    if (e->ev1) cudaEventDestroy(e->ev1);
+    if (e->own_stream && e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+static int engine_create_impl(gol_engine *e)
+{
+    const gol_config &cfg = e->cfg;
+    GOL_CUDA(cudaSetDevice(cfg.device));
+    cudaDeviceProp prop;
+    GOL_CUDA(cudaGetDeviceProperties(&prop, cfg.device));
+    e->num_sms = prop.multiProcessorCount;
+    GOL_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
+    e->own_stream = true;
+    GOL_CUDA(cudaEventCreate(&e->ev0));
+    GOL_CUDA(cudaEventCreate(&e->ev1));
+
+    if (!e->fast) {
+        const size_t bytes = (size_t)(gol_div_up(cfg.width, 64) * cfg.height) * sizeof(uint64_t);
+        for (auto &d : e->dense) {
+            GOL_CUDA(cudaMalloc(&d, bytes));
+            GOL_CUDA(cudaMemset(d, 0, bytes));
+        }
+        GOL_CUDA(cudaMalloc(&e->d_dflags, sizeof(uint32_t) * 2 * (kMaxBatch + 2)));
+        GOL_CUDA(cudaMallocHost(&e->h_dflags, sizeof(uint32_t) * 2 * (kMaxBatch + 2)));
+        return 0;
+    }
+
+    e->local.resize((size_t)e->per_proc);
+    e->max_strips = 1;
+    e->max_h = 1;
+    for (int i = 0; i < e->per_proc; ++i) {
+        LocalDomain &ld = e->local[(size_t)i];
+        ld.gid = e->rank * e->per_proc + i;
+        ld.r = ld.gid / e->C;
+        ld.c = ld.gid % e->C;
+        int64_t w, h;
+        domain_extent(e, ld.gid, &ld.x0, &ld.y0, &w, &h);
+        GOL_TRY(gol_layout_init(&ld.L, w, h));
+        GOL_TRY(gol_strip_geometry(ld.L.nw32, &ld.strips));
+    }
+    // launch geometry is uniform over all domains of the job (every process computes the same)
+    for (int g = 0; g < e->ndom; ++g) {
+        int64_t x0, y0, w, h;
+        domain_extent(e, g, &x0, &y0, &w, &h);
+        int s;
+        GOL_TRY(gol_strip_geometry(2 * (int)gol_div_up(w, 64), &s));
+        e->max_strips = std::max(e->max_strips, s);
+        e->max_h = std::max(e->max_h, h);
+    }
+    GOL_TRY(build_arena_layout(e, e->rank, &e->arena_layout));
+    GOL_CUDA(cudaMalloc(&e->arena, (size_t)e->arena_layout.total));
+    GOL_CUDA(cudaMemset(e->arena, 0, (size_t)e->arena_layout.total));
+    e->peer_arena.assign((size_t)e->P, nullptr);
+    e->peer_arena[(size_t)e->rank] = e->arena;
+    GOL_CUDA(cudaMalloc(&e->d_doms, sizeof(GolDomainDev) * (size_t)e->per_proc));
+    GOL_CUDA(cudaMalloc(&e->d_rec_tables, sizeof(void *) * (size_t)e->P));
+    GOL_CUDA(cudaMalloc(&e->d_results, sizeof(unsigned long long) * (kMaxBatch + 2)));
+    GOL_CUDA(cudaMemset(e->d_results, 0, sizeof(unsigned long long) * (kMaxBatch + 2)));
+    GOL_CUDA(cudaMallocHost(&e->h_results, sizeof(unsigned long long) * (kMaxBatch + 2)));
+    GOL_CUDA(cudaMalloc(&e->d_error, sizeof(unsigned int)));
+    GOL_CUDA(cudaMemset(e->d_error, 0, sizeof(unsigned int)));
+    if (e->P == 1) {
+        GOL_TRY(upload_domains(e));
+        e->imported = true;
+    }
+    return 0;
+}
+
+int gol_engine_create(const gol_config *cfg_in, gol_engine **out)
+{
+    if (!cfg_in || !out) GOL_FAIL("gol_engine_create: null argument");
+    gol_config cfg = *cfg_in;
+    if (cfg.width < 1 || cfg.height < 1)
+        GOL_FAIL("grid dimensions must be positive (got %lld x %lld)", (long long)cfg.width, (long long)cfg.height);
+    if (cfg.grid_rows < 1) cfg.grid_rows = 1;
+    if (cfg.grid_cols < 1) cfg.grid_cols = 1;
+    if (cfg.proc_count < 1) cfg.proc_count = 1;
+    if (cfg.gen_limit <= 0) cfg.gen_limit = GOL_DEFAULT_GEN_LIMIT;
+    if (cfg.similarity_frequency < 0) cfg.similarity_frequency = GOL_DEFAULT_SIMILARITY_FREQUENCY;
+    const int ndom = cfg.grid_rows * cfg.grid_cols;
+    if (ndom % cfg.proc_count) GOL_FAIL("%d domains cannot be dealt evenly to %d processes", ndom, cfg.proc_count);
+    if (cfg.proc_rank < 0 || cfg.proc_rank >= cfg.proc_count) GOL_FAIL("process rank %d out of range", cfg.proc_rank);
+
+    gol_engine *e = new gol_engine();
+    e->cfg = cfg;
+    e->R = cfg.grid_rows;
+    e->C = cfg.grid_cols;
+    e->ndom = ndom;
+    e->P = cfg.proc_count;
+    e->rank = cfg.proc_rank;
+    e->per_proc = ndom / cfg.proc_count;
+    // columns split at 64-cell boundaries, the remainder goes to the last column; rows evenly
+    const int64_t nq = gol_div_up(cfg.width, 64);
+    e->col_x.resize((size_t)e->C + 1);
+    for (int c = 0; c <= e->C; ++c) e->col_x[(size_t)c] = std::min<int64_t>(cfg.width, (nq * c / e->C) * 64);
+    e->col_x[(size_t)e->C] = cfg.width;
+    e->row_y.resize((size_t)e->R + 1);
+    for (int r = 0; r <= e->R; ++r) e->row_y[(size_t)r] = cfg.height * r / e->R;
+
+    bool fast = !(cfg.flags & GOL_FLAG_FORCE_GENERIC);
+    for (int g = 0; g < ndom && fast; ++g) {
+        int64_t x0, y0, w, h;
+        domain_extent(e, g, &x0, &y0, &w, &h);
+        if (w < GOL_MIN_FAST_WIDTH || h < GOL_MIN_FAST_HEIGHT) fast = false;
+    }
+    if (!fast && ndom > 1) {
+        delete e;
+        GOL_FAIL("grid %lld x %lld is too small for a %d x %d decomposition (every domain needs >= %d x %d cells)",
+                 (long long)cfg.width, (long long)cfg.height, cfg.grid_rows, cfg.grid_cols, GOL_MIN_FAST_WIDTH,
+                 GOL_MIN_FAST_HEIGHT);
+    }
+    e->fast = fast;
+    e->kmax = cfg.k_max > 0 ? cfg.k_max : 4;
+    if (e->kmax > GOL_GHOST_ROWS) e->kmax = GOL_GHOST_ROWS;
+    int kk = 1;
+    while (kk * 2 <= e->kmax) kk *= 2;
+    e->kmax = kk;
+    e->batch = cfg.batch_gens > 0 ? cfg.batch_gens : 128;
+    if (e->batch > kMaxBatch) e->batch = kMaxBatch;
+
+    if (engine_create_impl(e)) {
+        gol_engine_destroy(e);
+        return 1;
+    }
+    *out = e;
+    return 0;
+}
+
+int gol_engine_set_stream(gol_engine *e, void *stream)
+{
+    GOL_CUDA(cudaStreamSynchronize(e->stream));
+    if (e->own_stream) cudaStreamDestroy(e->stream);
+    e->own_stream = false;
+    e->stream = (cudaStream_t)stream;
+    return 0;
+}
+
+int gol_engine_num_domains(const gol_engine *e) { return e->ndom; }
+int gol_engine_num_local_domains(const gol_engine *e) { return e->per_proc; }
+int gol_engine_local_domain_id(const gol_engine *e, int i) { return e->rank * e->per_proc + i; }
+int gol_engine_uses_fast_path(const gol_engine *e) { return e->fast ? 1 : 0; }
+
+int gol_engine_domain_extent(const gol_engine *e, int gid, int64_t *x0, int64_t *y0, int64_t *w, int64_t *h)
+{
+    if (gid < 0 || gid >= e->ndom) GOL_FAIL("domain id %d out of range", gid);
+    domain_extent(e, gid, x0, y0, w, h);
+    return 0;
+}
+
+int gol_engine_domain_neighbors(const gol_engine *e, int gid, int32_t nb[8])
+{
+    if (gid < 0 || gid >= e->ndom) GOL_FAIL("domain id %d out of range", gid);
+    for (int d = 0; d < GOL_NDIR; ++d) nb[d] = neighbor_gid(e, gid, d);
+    return 0;
+}
+
+size_t gol_engine_ipc_blob_size(const gol_engine *) { return sizeof(IpcBlob); }
+
+int gol_engine_ipc_export(gol_engine *e, void *blob)
+{
+    if (!e->fast) GOL_FAIL("gol_engine_ipc_export: engine is on the single-domain generic path");
+    GOL_CUDA(cudaSetDevice(e->cfg.device));
+    IpcBlob b;
+    memset(&b, 0, sizeof b);
+    GOL_CUDA(cudaIpcGetMemHandle(&b.handle, e->arena));
+    b.device = e->cfg.device;
+    b.pid = (int32_t)getpid();
+    b.arena_bytes = e->arena_layout.total;
+    memcpy(blob, &b, sizeof b);
+    return 0;
+}
+
+int gol_engine_ipc_import(gol_engine *e, const void *all_blobs)
+{
+    if (!e->fast) GOL_FAIL("gol_engine_ipc_import: engine is on the single-domain generic path");
+    GOL_CUDA(cudaSetDevice(e->cfg.device));
+    const IpcBlob *blobs = static_cast<const IpcBlob *>(all_blobs);
+    for (int p = 0; p < e->P; ++p) {
+        if (p == e->rank) continue;
+        IpcBlob b;
+        memcpy(&b, blobs + p, sizeof b);
+        ArenaLayout A;
+        GOL_TRY(build_arena_layout(e, p, &A));
+        if (A.total != b.arena_bytes)
+            GOL_FAIL("process %d reports a %lld-byte arena, expected %lld: configurations differ", p,
+                     (long long)b.arena_bytes, (long long)A.total);
+        void *ptr = nullptr;
+        GOL_CUDA(cudaIpcOpenMemHandle(&ptr, b.handle, cudaIpcMemLazyEnablePeerAccess));
+        e->peer_arena[(size_t)p] = static_cast<char *>(ptr);
+    }
+    GOL_TRY(upload_domains(e));
+    e->imported = true;
+    return 0;
+}
+
+// -------------------------------------------------------------- load / store
+static int clear_current(gol_engine *e)
+{
+    e->prepared = false;
+    if (!e->fast) {
+        e->cur = 0;
+        return 0;
+    }
+    return 0;
+}
+
+int gol_engine_load_packed(gol_engine *e, const uint64_t *host)
+{
+    GOL_CUDA(cudaSetDevice(e->cfg.device));
+    GOL_TRY(clear_current(e));
+    const int64_t nqg = gol_div_up(e->cfg.width, 64);
+    if (!e->fast) {
+        GOL_CUDA(cudaMemcpyAsync(e->dense[e->cur], host, (size_t)(nqg * e->cfg.height) * 8, cudaMemcpyHostToDevice,
+                                 e->stream));
+        GOL_CUDA(cudaStreamSynchronize(e->stream));
+        return 0;
+    }
+    for (int i = 0; i < e->per_proc; ++i) {
+        const LocalDomain &ld = e->local[(size_t)i];
+        char *dst = e->arena + e->arena_layout.buf_off[(size_t)i * GOL_NBUF + e->cur];
+        GOL_CUDA(cudaMemsetAsync(dst, 0, (size_t)ld.L.buffer_words32 * 4, e->stream));
+        GOL_CUDA(cudaMemcpy2DAsync(dst + ((int64_t)G * ld.L.pitch32 + GOL_GHOST_WORDS32) * 4, (size_t)ld.L.pitch32 * 4,
+                                   host + ld.y0 * nqg + ld.x0 / 64, (size_t)nqg * 8, (size_t)ld.L.nq * 8,
+                                   (size_t)ld.L.height, cudaMemcpyHostToDevice, e->stream));
+    }
+    GOL_CUDA(cudaStreamSynchronize(e->stream));
+    return 0;
+}
+
+int gol_engine_load_packed_device(gol_engine *e, const uint64_t *d_packed, int64_t x0, int64_t y0, int64_t w,
+                                  int64_t h)
+{
+    GOL_CUDA(cudaSetDevice(e->cfg.device));
+    GOL_TRY(clear_current(e));
+    const int64_t nq = gol_div_up(w, 64);
+    if (!e->fast) {
+        if (x0 || y0 || w != e->cfg.width || h != e->cfg.height) GOL_FAIL("load_packed_device: block must be the whole grid");
+        GOL_CUDA(cudaMemcpyAsync(e->dense[e->cur], d_packed, (size_t)(nq * h) * 8, cudaMemcpyDeviceToDevice, e->stream));
+        return 0;
+    }
+    for (int i = 0; i < e->per_proc; ++i) {
+        const LocalDomain &ld = e->local[(size_t)i];
+        if (ld.x0 != x0 || ld.y0 != y0) continue;
+        if (ld.L.width != w || ld.L.height != h) GOL_FAIL("load_packed_device: block does not match domain %d", ld.gid);
+        char *dst = e->arena + e->arena_layout.buf_off[(size_t)i * GOL_NBUF + e->cur];
+        GOL_CUDA(cudaMemsetAsync(dst, 0, (size_t)ld.L.buffer_words32 * 4, e->stream));
+        GOL_TRY(gol_launch_dense_to_padded(d_packed, nq, 0, reinterpret_cast<uint32_t *>(dst), ld.L, e->stream));
+        ++e->launches;
+        return 0;
+    }
+    GOL_FAIL("load_packed_device: no local domain starts at (%lld, %lld)", (long long)x0, (long long)y0);
+}
+
+int gol_engine_randomize(gol_engine *e, uint64_t seed)
+{
+    GOL_CUDA(cudaSetDevice(e->cfg.device));
+    GOL_TRY(clear_current(e));
+    if (!e->fast) {
+        GOL_TRY(gol_op_random_dense(e->dense[e->cur], e->cfg.width, e->cfg.height, 0, 0, seed, e->stream));
+        ++e->launches;
+        return 0;
+    }
+    for (int i = 0; i < e->per_proc; ++i) {
+        const LocalDomain &ld = e->local[(size_t)i];
+        uint64_t *tmp = nullptr;
+        GOL_CUDA(cudaMalloc(&tmp, (size_t)ld.L.nq * (size_t)ld.L.height * 8));
+        int rc = gol_op_random_dense(tmp, ld.L.width, ld.L.height, ld.x0, ld.y0, seed, e->stream);
+        char *dst = e->arena + e->arena_layout.buf_off[(size_t)i * GOL_NBUF + e->cur];
+        if (!rc) rc = cudaMemsetAsync(dst, 0, (size_t)ld.L.buffer_words32 * 4, e->stream) != cudaSuccess;
+        if (!rc) rc = gol_launch_dense_to_padded(tmp, ld.L.nq, 0, reinterpret_cast<uint32_t *>(dst), ld.L, e->stream);
+        e->launches += 2;
+        cudaStreamSynchronize(e->stream);
+        cudaFree(tmp);
+        if (rc) return 1;
+    }
+    return 0;
+}
+
+int gol_engine_download_packed(gol_engine *e, uint64_t *host)
+{
+    GOL_CUDA(cudaSetDevice(e->cfg.device));
+    const int64_t nqg = gol_div_up(e->cfg.width, 64);
+    if (!e->fast) {
+        GOL_CUDA(cudaMemcpyAsync(host, e->dense[e->cur], (size_t)(nqg * e->cfg.height) * 8, cudaMemcpyDeviceToHost,
+                                 e->stream));
+        GOL_CUDA(cudaStreamSynchronize(e->stream));
+        return 0;
+    }
+    for (int i = 0; i < e->per_proc; ++i) {
+        const LocalDomain &ld = e->local[(size_t)i];
+        const char *src = e->arena + e->arena_layout.buf_off[(size_t)i * GOL_NBUF + e->cur];
+        GOL_CUDA(cudaMemcpy2DAsync(host + ld.y0 * nqg + ld.x0 / 64, (size_t)nqg * 8,
+                                   src + ((int64_t)G * ld.L.pitch32 + GOL_GHOST_WORDS32) * 4, (size_t)ld.L.pitch32 * 4,
+                                   (size_t)ld.L.nq * 8, (size_t)ld.L.height, cudaMemcpyDeviceToHost, e->stream));
+    }
+    GOL_CUDA(cudaStreamSynchronize(e->stream));
+    return 0;
+}
+
+// Parallel text read: every process reads only its own byte ranges.  The file must be in
+// the fixed-record layout (height lines of exactly width cells + '\n'), which is what
+// generate.sh and every writer of the reference produce; other layouts go through
+// gol_file_read_packed (host filter with the fgetc semantics) + gol_engine_load_packed.
+int gol_engine_load_text_file(gol_engine *e, const char *path, int strict)
+{
+    GOL_CUDA(cudaSetDevice(e->cfg.device));
+    const int64_t W = e->cfg.width, H = e->cfg.height;
+    int fd = open(path, O_RDONLY);
+    if (fd < 0) GOL_FAIL("fopen: %s: %s", path, strerror(errno));
+    struct stat st;
+    if (fstat(fd, &st) != 0) {
+        close(fd);
+        GOL_FAIL("fstat: %s: %s", path, strerror(errno));
+    }
+    const bool fixed = st.st_size == H * (W + 1) || st.st_size == H * (W + 1) - 1;
+    if (!fixed) {
+        close(fd);
+        if ((int64_t)st.st_size < W * H)
+            GOL_FAIL("input is too short: %s has %lld bytes, a %lld x %lld grid needs at least %lld", path,
+                     (long long)st.st_size, (long long)W, (long long)H, (long long)(W * H));
+        if ((int64_t)st.st_size > (1ll << 32))
+            GOL_FAIL("%s is not in fixed-record layout (%lld bytes, expected %lld) and too large for the host filter",
+                     path, (long long)st.st_size, (long long)(H * (W + 1)));
+        std::vector<uint64_t> packed((size_t)(gol_div_up(W, 64) * H));
+        GOL_TRY(gol_file_read_packed(path, W, H, strict, packed.data()));
+        return gol_engine_load_packed(e, packed.data());
+    }
+    GOL_TRY(clear_current(e));
+    int rc = 0;
+    const int ndom_local = e->fast ? e->per_proc : 1;
+    for (int i = 0; i < ndom_local && !rc; ++i) {
+        int64_t x0 = 0, y0 = 0, w = W, h = H;
+        if (e->fast) {
+            const LocalDomain &ld = e->local[(size_t)i];
+            x0 = ld.x0; y0 = ld.y0; w = ld.L.width; h = ld.L.height;
+        }
+        const bool last_col = x0 + w == W;
+        const int64_t seg = w + (last_col ? 1 : 0);  // bytes per row of this domain (newline owned by last column)
+        const int64_t rows_per = std::max<int64_t>(1, std::min<int64_t>(h, (64ll << 20) / seg));
+        char *h_stage = nullptr, *d_stage = nullptr;
+        uint64_t *d_dense = nullptr;
+        uint32_t *d_err = nullptr;
+        const int64_t nq = gol_div_up(w, 64);
+        if (cudaMallocHost(&h_stage, (size_t)(rows_per * seg)) != cudaSuccess ||
+            cudaMalloc(&d_stage, (size_t)(rows_per * seg)) != cudaSuccess ||
+            cudaMalloc(&d_dense, (size_t)(nq * h) * 8) != cudaSuccess || cudaMalloc(&d_err, 4) != cudaSuccess) {
+            gol_set_error("out of memory staging %s", path);
+            rc = 1;
+        }
+        if (!rc) cudaMemsetAsync(d_err, 0, 4, e->stream);
+        for (int64_t r = 0; r < h && !rc; r += rows_per) {
+            const int64_t n = std::min(rows_per, h - r);
+            if (x0 == 0 && last_col) {
+                // whole rows: one contiguous range
+                int64_t want = n * seg;
+                if ((y0 + r + n) * (W + 1) > st.st_size) want = st.st_size - (y0 + r) * (W + 1);  // no final newline
+                int64_t off = 0;
+                while (off < want) {
+                    ssize_t got = pread(fd, h_stage + off, (size_t)(want - off), (off_t)((y0 + r) * (W + 1) + off));
+                    if (got <= 0) { if (got < 0 && errno == EINTR) continue; gol_set_error("read: %s: %s", path, got < 0 ? strerror(errno) : "unexpected end of file"); rc = 1; break; }
+                    off += got;
+                }
+                if (want < n * seg) h_stage[n * seg - 1] = '\n';
+            } else {
+                for (int64_t k = 0; k < n && !rc; ++k) {
+                    int64_t want = seg;
+                    const int64_t pos = (y0 + r + k) * (W + 1) + x0;
+                    if (pos + want > st.st_size) { want = st.st_size - pos; h_stage[k * seg + seg - 1] = '\n'; }
+                    int64_t off = 0;
+                    while (off < want) {
+                        ssize_t got = pread(fd, h_stage + k * seg + off, (size_t)(want - off), (off_t)(pos + off));
+                        if (got <= 0) { if (got < 0 && errno == EINTR) continue; gol_set_error("read: %s: %s", path, got < 0 ? strerror(errno) : "unexpected end of file"); rc = 1; break; }
+                        off += got;
+                    }
+                }
+            }
+            if (rc) break;
+            if (cudaMemcpyAsync(d_stage, h_stage, (size_t)(n * seg), cudaMemcpyHostToDevice, e->stream) != cudaSuccess) { gol_set_error("H2D copy failed"); rc = 1; break; }
+            rc = gol_op_parse_text(d_stage, d_dense + r * nq, w, n, seg, d_err, e->stream);
+            ++e->launches;
+            if (!rc && cudaStreamSynchronize(e->stream) != cudaSuccess) { gol_set_error("parse kernel failed: %s", cudaGetErrorString(cudaGetLastError())); rc = 1; }
+        }
+        if (!rc) {
+            uint32_t err = 0;
+            cudaMemcpy(&err, d_err, 4, cudaMemcpyDeviceToHost);
+            if ((err & 2) || ((err & 1) && strict)) {
+                gol_set_error("%s: %s", path, (err & 2) ? "a line does not end in a newline at column width (garbled record layout)"
+                                                       : "invalid byte: only '0', '1' and newlines are accepted");
+                rc = 1;
+            }
+        }
+        if (!rc) {
+            if (e->fast) {
+                const LocalDomain &ld = e->local[(size_t)i];
+                char *dst = e->arena + e->arena_layout.buf_off[(size_t)i * GOL_NBUF + e->cur];
+                if (cudaMemsetAsync(dst, 0, (size_t)ld.L.buffer_words32 * 4, e->stream) != cudaSuccess) rc = 1;
+                if (!rc) rc = gol_launch_dense_to_padded(d_dense, nq, 0, reinterpret_cast<uint32_t *>(dst), ld.L, e->stream);
+                ++e->launches;
+            } else {
+                if (cudaMemcpyAsync(e->dense[e->cur], d_dense, (size_t)(nq * h) * 8, cudaMemcpyDeviceToDevice, e->stream) != cudaSuccess) rc = 1;
+            }
+            cudaStreamSynchronize(e->stream);
+        }
+        if (h_stage) cudaFreeHost(h_stage);
+        if (d_stage) cudaFree(d_stage);
+        if (d_dense) cudaFree(d_dense);
+        if (d_err) cudaFree(d_err);
+    }
+    close(fd);
+    return rc;
+}
+
+int gol_engine_store_text_file(gol_engine *e, const char *path)
+{
+    GOL_CUDA(cudaSetDevice(e->cfg.device));
+    const int64_t W = e->cfg.width, H = e->cfg.height;
+    int fd = open(path, O_WRONLY | O_CREAT, 0644);
+    if (fd < 0) GOL_FAIL("fopen: %s: %s", path, strerror(errno));
+    if (ftruncate(fd, (off_t)(H * (W + 1))) != 0) {
+        close(fd);
+        GOL_FAIL("ftruncate: %s: %s", path, strerror(errno));
+    }
+    int rc = 0;
+    const int ndom_local = e->fast ? e->per_proc : 1;
+    for (int i = 0; i < ndom_local && !rc; ++i) {
+        int64_t x0 = 0, y0 = 0, w = W, h = H;
+        if (e->fast) {
+            const LocalDomain &ld = e->local[(size_t)i];
+            x0 = ld.x0; y0 = ld.y0; w = ld.L.width; h = ld.L.height;
+        }
+        const bool last_col = x0 + w == W;
+        const int64_t seg = w + (last_col ? 1 : 0);
+        const int64_t rows_per = std::max<int64_t>(1, std::min<int64_t>(h, (64ll << 20) / seg));
+        const int64_t nq = gol_div_up(w, 64);
+        char *h_stage = nullptr, *d_stage = nullptr;
+        uint64_t *d_dense = nullptr;
+        if (cudaMallocHost(&h_stage, (size_t)(rows_per * seg)) != cudaSuccess ||
+            cudaMalloc(&d_stage, (size_t)(rows_per * seg)) != cudaSuccess) {
+            gol_set_error("out of memory staging %s", path);
+            rc = 1;
+        }
+        const uint64_t *dense = nullptr;
+        if (!rc) {
+            if (e->fast) {
+                const LocalDomain &ld = e->local[(size_t)i];
+                if (cudaMalloc(&d_dense, (size_t)(nq * h) * 8) != cudaSuccess) { gol_set_error("out of memory"); rc = 1; }
+                const char *src = e->arena + e->arena_layout.buf_off[(size_t)i * GOL_NBUF + e->cur];
+                if (!rc) rc = gol_launch_padded_to_dense(reinterpret_cast<const uint32_t *>(src), ld.L, d_dense, nq, 0, 0, e->stream);
+                ++e->launches;
+                dense = d_dense;
+            } else {
+                dense = e->dense[e->cur];
+            }
+        }
+        for (int64_t r = 0; r < h && !rc; r += rows_per) {
+            const int64_t n = std::min(rows_per, h - r);
+            rc = gol_op_format_text(dense + r * nq, d_stage, w, n, seg, last_col ? 1 : 0, e->stream);
+            ++e->launches;
+            if (!rc && (cudaMemcpyAsync(h_stage, d_stage, (size_t)(n * seg), cudaMemcpyDeviceToHost, e->stream) != cudaSuccess ||
+                        cudaStreamSynchronize(e->stream) != cudaSuccess)) {
+                gol_set_error("format kernel / D2H copy failed: %s", cudaGetErrorString(cudaGetLastError()));
+                rc = 1;
+            }
+            if (rc) break;
+            if (x0 == 0 && last_col) {
+                rc = gol_write_all(fd, h_stage, (size_t)(n * seg), (y0 + r) * (W + 1), path);
+            } else {
+                for (int64_t k = 0; k < n && !rc; ++k)
+                    rc = gol_write_all(fd, h_stage + k * seg, (size_t)seg, (y0 + r + k) * (W + 1) + x0, path);
+            }
+        }
+        if (h_stage) cudaFreeHost(h_stage);
+        if (d_stage) cudaFree(d_stage);
+        if (d_dense) cudaFree(d_dense);
+    }
+    close(fd);
+    return rc;
+}
+
+// ------------------------------------------------------------------- driver
+int gol_engine_prepare(gol_engine *e)
+{
+    GOL_CUDA(cudaSetDevice(e->cfg.device));
+    GOL_TRY(check_ready(e, "gol_engine_prepare"));
+    if (e->fast) {
+        GolLaunch lp{};
+        geometry(e, 1, &lp);
+        lp.in_idx = e->cur;
+        lp.out_idx = e->cur;
+        lp.wait_seq = 0;
+        lp.seq = ++e->seq;
+        lp.signal = multi(e) ? 1 : 0;
+        lp.rec_slot = -1;
+        GOL_TRY(gol_launch_halo(e->d_doms, e->per_proc, lp, 0, e->stream));
+        ++e->launches;
+    }
+    e->prepared = true;
+    return 0;
+}
+
+int gol_engine_step(gol_engine *e, int64_t n)
+{
+    GOL_CUDA(cudaSetDevice(e->cfg.device));
+    GOL_TRY(check_ready(e, "gol_engine_step"));
+    if (!e->prepared) GOL_TRY(gol_engine_prepare(e));
+    GOL_CUDA(cudaEventRecord(e->ev0, e->stream));
+    if (e->fast) {
+        GOL_TRY(run_epochs(e, n, -1, false, false, e->kmax));
+    } else {
+        for (int64_t left = n; left > 0; left -= kMaxBatch) GOL_TRY(dense_steps(e, (int)std::min<int64_t>(left, kMaxBatch), false));
+    }
+    GOL_CUDA(cudaEventRecord(e->ev1, e->stream));
+    GOL_CUDA(cudaEventSynchronize(e->ev1));
+    float ms = 0;
+    GOL_CUDA(cudaEventElapsedTime(&ms, e->ev0, e->ev1));
+    e->last_ms = ms;
+    if (e->fast) {
+        unsigned int err = 0;
+        GOL_CUDA(cudaMemcpy(&err, e->d_error, 4, cudaMemcpyDeviceToHost));
+        if (err) GOL_FAIL("device-side wait timed out (code %u)", err);
+    }
+    return 0;
+}
+
+int gol_engine_run(gol_engine *e, gol_result *res)
+{
+    GOL_CUDA(cudaSetDevice(e->cfg.device));
+    GOL_TRY(check_ready(e, "gol_engine_run"));
+    if (!e->prepared) GOL_TRY(gol_engine_prepare(e));
+    GOL_TRY(e->fast ? run_fast(e, res) : run_dense(e, res));
+    if (res) GOL_TRY(fill_population(e, res));
+    return 0;
+}
+
+int gol_engine_sync(gol_engine *e)
+{
+    GOL_CUDA(cudaSetDevice(e->cfg.device));
+    GOL_CUDA(cudaStreamSynchronize(e->stream));
+    return 0;
+}
+
+int64_t gol_engine_launch_count(const gol_engine *e) { return e->launches; }
+double gol_engine_last_ms(const gol_engine *e) { return e->last_ms; }
+
+int gol_engine_population(gol_engine *e, uint64_t *count)
+{
+    GOL_CUDA(cudaSetDevice(e->cfg.device));
+    unsigned long long *d_count = nullptr;
+    GOL_CUDA(cudaMalloc(&d_count, 8));
+    cudaMemsetAsync(d_count, 0, 8, e->stream);
+    int rc = 0;
+    if (!e->fast) {
+        rc = gol_op_popcount_dense(e->dense[e->cur], e->cfg.width, e->cfg.height, d_count, e->stream);
+        ++e->launches;
+    } else {
+        for (int i = 0; i < e->per_proc && !rc; ++i) {
+            const LocalDomain &ld = e->local[(size_t)i];
+            uint64_t *tmp = nullptr;
+            if (cudaMalloc(&tmp, (size_t)ld.L.nq * (size_t)ld.L.height * 8) != cudaSuccess) { gol_set_error("out of memory"); rc = 1; break; }
+            const char *src = e->arena + e->arena_layout.buf_off[(size_t)i * GOL_NBUF + e->cur];
+            rc = gol_launch_padded_to_dense(reinterpret_cast<const uint32_t *>(src), ld.L, tmp, ld.L.nq, 0, 0, e->stream);
+            if (!rc) rc = gol_op_popcount_dense(tmp, ld.L.width, ld.L.height, d_count, e->stream);
+            e->launches += 2;
+            cudaStreamSynchronize(e->stream);
+            cudaFree(tmp);
+        }
+    }
+    unsigned long long c = 0;
+    if (!rc && cudaMemcpyAsync(&c, d_count, 8, cudaMemcpyDeviceToHost, e->stream) != cudaSuccess) rc = 1;
+    cudaStreamSynchronize(e->stream);
+    cudaFree(d_count);
+    *count = c;
+    return rc;
+}
+
+int gol_engine_domain_buffer(gol_engine *e, int i, void **d_ptr, gol_layout *layout)
+{
+    if (!e->fast) {
+        if (i != 0) GOL_FAIL("domain index %d out of range", i);
+        *d_ptr = e->dense[e->cur];
+        GOL_TRY(gol_layout_init(layout, e->cfg.width, e->cfg.height));
+        layout->ghost_rows = 0;       // dense buffer: no padding at all
+        layout->pitch32 = layout->nw32;
+        layout->rows_padded = layout->height;
+        layout->buffer_words32 = layout->rows_padded * layout->pitch32;
+        return 0;
+    }
+    if (i < 0 || i >= e->per_proc) GOL_FAIL("domain index %d out of range", i);
+    *d_ptr = e->arena + e->arena_layout.buf_off[(size_t)i * GOL_NBUF + e->cur];
+    *layout = e->local[(size_t)i].L;
+    return 0;
+}
+
+}  // extern "C"

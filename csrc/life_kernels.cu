@@ -1,0 +1,541 @@
+// Generation kernels for sm_100a.
+//
+//  life_strip_kernel<K, FLAGS>  — the product kernel.  One warp owns a vertical strip of the
+//      padded bit grid (32 lanes x 64 cells, the two outer lanes are a redundant apron) and
+//      streams down the rows.  K generations are pipelined in registers (temporal blocking):
+//      level t consumes the row produced by level t-1 one step earlier, so a row is read from
+//      memory once and written once per K generations.  Neighbour words move between lanes
+//      with warp shuffles; the B3/S23 rule is a 10-LOP3 bit-sliced adder per 32 cells.
+//      The same kernel pushes its border rows/columns straight into the neighbours' ghost
+//      zones (its own for a single torus domain, peer-mapped memory over NVLink otherwise),
+//      publishes release flags, and (FLAGS) reduces the alive / changed bits of the last level.
+//      Replaces evolve (S:60-101, C:27-53, O:29-57, G:128-148), halo_rows/halo_cols (G:52-74),
+//      the MPI halo exchange (C:280-344), compare/similarity (G:76-100, C:83-109) and
+//      empty (G:102-126, C:55-81).
+//  halo_push_kernel — the border push alone (first exchange after a load).
+//  gather_flags_kernel — flag all-reduce: waits for every domain's record of a batch.
+//  dense kernels — generic 1-generation torus step for any size (tiny grids, PyTorch op).
+#include <cuda_runtime.h>
+
+#include <type_traits>
+
+#include "gol_internal.h"
+
+namespace {
+
+constexpr int kWarps = 4;           // warps per CTA
+constexpr int kWL = 2;              // 32-bit words per lane (64 cells)
+constexpr int kValidLanes = 30;     // lanes 1..30 own output, lanes 0 and 31 are apron
+constexpr int kVW = kValidLanes * kWL;  // owned words per strip
+constexpr int G = GOL_GHOST_ROWS;
+
+// First owned word of a strip.  Strips are 60 words wide; the last one is right-aligned to the
+// row end (it may overlap its left neighbour, which then computes identical words twice) so
+// that it always owns the row's last 128 cells, which it pushes east.
+__device__ __forceinline__ int strip_origin(int strip, int S, int nw)
+{
+    return (strip == S - 1 && S > 1) ? nw - kVW : strip * kVW;
+}
+
+template <int LUT>
+__device__ __forceinline__ uint32_t lop3(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, %4;" : "=r"(d) : "r"(a), "r"(b), "r"(c), "n"(LUT));
+    return d;
+}
+__device__ __forceinline__ uint32_t xor3(uint32_t a, uint32_t b, uint32_t c) { return lop3<0x96>(a, b, c); }
+__device__ __forceinline__ uint32_t maj3(uint32_t a, uint32_t b, uint32_t c) { return lop3<0xE8>(a, b, c); }
+
+// Next state of 32 cells from the bit-sliced 3-cell row sums (s0 + 2*s1, centre included) of
+// the rows above (a), at (b) and below (n) and the centre word m.  T = 9-cell sum:
+// alive' = (T == 3) | (m & T == 4).
+__device__ __forceinline__ uint32_t life_rule(uint32_t a0, uint32_t a1, uint32_t b0, uint32_t b1,
+                                              uint32_t n0, uint32_t n1, uint32_t m)
+{
+    const uint32_t x0 = xor3(a0, b0, n0);
+    const uint32_t k0 = maj3(a0, b0, n0);
+    const uint32_t x1 = xor3(a1, b1, n1);
+    const uint32_t k1 = maj3(a1, b1, n1);
+    const uint32_t g = lop3<0x14>(k0, x1, k1);   // (k0 ^ x1) & ~k1            : T in {2,3}
+    const uint32_t h = lop3<0x42>(k0, x1, k1);   // ~(k0 ^ x1) & (k1 ^ (k0&x1)) : T in {4,5}
+    const uint32_t u = lop3<0x08>(x0, h, m);     // ~x0 & h & m                 : T == 4, alive
+    return lop3<0xEA>(x0, g, u);                 // (x0 & g) | u
+}
+
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p)
+{
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v)
+{
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys64(const unsigned long long *p)
+{
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// ---------------------------------------------------------------- border push
+// Copies the border rows / columns of rows [y0,y1) of buffer `o` owned by `strip` into the
+// ghost zones of the 8 neighbours.  Executed by one warp; reads data this warp wrote earlier.
+__device__ void push_borders(const GolDomainDev &D, int o, int strip, int y0, int y1, int lane)
+{
+    const int H = D.H, nw = D.nw32, pitch = D.pitch32;
+    const uint32_t *src = D.buf[o];
+    const int lo = strip_origin(strip, D.strips, nw), hi = min(nw, lo + kVW);
+
+    // rows -> north / south neighbours' ghost rows
+    for (int pass = 0; pass < 2; ++pass) {
+        const int dir = pass;  // 0 = N, 1 = S
+        const int ya = pass == 0 ? y0 : max(y0, H - G);
+        const int yb = pass == 0 ? min(y1, G) : y1;
+        if (ya >= yb) continue;
+        const GolNeighbor &nb = D.nb[dir];
+        for (int y = ya; y < yb; ++y) {
+            const int drow = pass == 0 ? (G + nb.H + y) : (G + y - H);
+            const uint32_t *s = src + (int64_t)(y + G) * pitch + GOL_GHOST_WORDS32;
+            uint32_t *d = nb.buf[o] + (int64_t)drow * nb.pitch32 + GOL_GHOST_WORDS32;
+            for (int i = lo + 2 * lane; i < hi; i += 64)
+                *reinterpret_cast<uint2 *>(d + i) = *reinterpret_cast<const uint2 *>(s + i);
+        }
+    }
+
+    const bool first = strip == 0, last = strip == D.strips - 1;
+    if (!first && !last) return;
+    const int W_cells = D.nwf32 * 32 + D.rem;
+    for (int y = y0 + lane; y < y1; y += 32) {
+        const uint32_t *s = src + (int64_t)(y + G) * pitch + GOL_GHOST_WORDS32;
+        if (first) {
+            // my first cells -> west neighbours' right ghost slot, pre-shifted by their width % 64
+            const uint32_t w0 = s[0], w1 = s[1], w2 = s[2], w3 = s[3];
+            for (int v = 0; v < 3; ++v) {  // W, NW, SW
+                int dir, drow;
+                if (v == 0) { dir = 2; drow = G + y; }
+                else if (v == 1) { if (y >= G) continue; dir = 4; drow = G + D.nb[4].H + y; }
+                else { if (y < H - G) continue; dir = 6; drow = G + y - H; }
+                const GolNeighbor &nb = D.nb[dir];
+                const int sh = nb.rem, ws = sh >> 5, bs = sh & 31;
+                uint32_t in[4] = {w0, w1, w2, w3}, outw[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    uint32_t val = 0;
+                    const int a = j - ws;
+                    if (a >= 0) val = in[a] << bs;
+                    if (bs && a - 1 >= 0) val |= in[a - 1] >> (32 - bs);
+                    outw[j] = val;
+                }
+                uint32_t *d = nb.buf[o] + (int64_t)drow * nb.pitch32 + GOL_GHOST_WORDS32 + nb.nw32;
+                d[0] = outw[0]; d[1] = outw[1]; d[2] = outw[2]; d[3] = outw[3];
+            }
+        }
+        if (last) {
+            // my last 128 cells -> east neighbours' left ghost slot
+            uint32_t outw[4];
+            const int ob = W_cells - 128;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int bp = ob + 32 * j, wi = bp >> 5, bo = bp & 31;
+                uint32_t val = s[wi] >> bo;
+                if (bo && wi + 1 < nw) val |= s[wi + 1] << (32 - bo);
+                outw[j] = val;
+            }
+            for (int v = 0; v < 3; ++v) {  // E, NE, SE
+                int dir, drow;
+                if (v == 0) { dir = 3; drow = G + y; }
+                else if (v == 1) { if (y >= G) continue; dir = 5; drow = G + D.nb[5].H + y; }
+                else { if (y < H - G) continue; dir = 7; drow = G + y - H; }
+                const GolNeighbor &nb = D.nb[dir];
+                uint32_t *d = nb.buf[o] + (int64_t)drow * nb.pitch32;
+                d[0] = outw[0]; d[1] = outw[1]; d[2] = outw[2]; d[3] = outw[3];
+            }
+        }
+    }
+}
+
+// Spin until the 8 neighbours have published sequence >= want into my epoch flags.
+__device__ void wait_neighbors(const GolDomainDev &D, uint32_t want, int lane)
+{
+    if (lane < GOL_NDIR) {
+        const uint32_t *f = D.epoch_flags + lane;
+        long long t0 = clock64();
+        while ((int32_t)(ld_acquire_sys(f) - want) < 0) {
+            if (clock64() - t0 > (1ll << 33)) {  // ~4 s: neighbour is gone
+                atomicOr(&D.scratch->error, 1u);
+                break;
+            }
+            __nanosleep(64);
+        }
+    }
+    __syncwarp();
+    __threadfence();  // acquire for the whole warp: drop stale L1 lines of the ghost zones
+}
+
+// CTA epilogue: count finished CTAs of this domain; the last one publishes records and flags.
+__device__ void finish_domain(const GolDomainDev &D, const GolLaunch &lp)
+{
+    __syncthreads();
+    if (threadIdx.x != 0) return;
+    __threadfence_system();
+    const unsigned prev = atomicAdd(&D.scratch->done, 1u);
+    if (prev != (unsigned)lp.ctas_per_domain - 1) return;
+    __threadfence_system();
+    if (lp.rec_slot >= 0) {
+        const unsigned a = atomicExch(&D.scratch->alive, 0u);
+        const unsigned d = atomicExch(&D.scratch->diff, 0u);
+        const unsigned long long rec =
+            ((unsigned long long)lp.rec_seq << 32) | (a ? 1ull : 0ull) | (d ? 2ull : 0ull);
+        for (int p = 0; p < D.proc_count; ++p) {
+            unsigned long long *t = D.rec_tables[p] + (int64_t)lp.rec_slot * D.num_domains + D.global_id;
+            asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(t), "l"(rec) : "memory");
+        }
+    }
+    if (lp.signal)
+        for (int d = 0; d < GOL_NDIR; ++d) st_release_sys(D.nb[d].flag, lp.seq);
+    D.scratch->done = 0;
+    __threadfence();
+}
+
+// ------------------------------------------------------------- strip kernel
+template <int K, bool FLAGS>
+__global__ void __launch_bounds__(kWarps * 32) life_strip_kernel(const GolDomainDev *__restrict__ doms,
+                                                                 const GolLaunch lp)
+{
+    const int dom_id = blockIdx.x / lp.ctas_per_domain;
+    const int cta = blockIdx.x - dom_id * lp.ctas_per_domain;
+    const GolDomainDev &D = doms[dom_id];
+    const int lane = threadIdx.x & 31;
+    const int item = cta * kWarps + (threadIdx.x >> 5);
+    const int S = D.strips;
+    const int strip = item % S, chunk = item / S;
+    const int H = D.H;
+    const int y0 = chunk * lp.chunk_rows;
+    const int y1 = min(H, y0 + lp.chunk_rows);
+    const bool need_done = lp.signal || lp.rec_slot >= 0;
+
+    if (chunk < lp.chunks && y0 < H) {
+        const int nw = D.nw32, nwf = D.nwf32, rem = D.rem, pitch = D.pitch32;
+        const uint32_t *__restrict__ in = D.buf[lp.in_idx];
+        uint32_t *__restrict__ out = D.buf[lp.out_idx];
+        const int vi = strip_origin(strip, S, nw) - kWL + lane * kWL;  // virtual index of this lane's first word
+        const bool reads_ghosts = strip == 0 || strip == S - 1 || y0 - K < 0 || y1 + K > H;
+        const bool border = strip == 0 || strip == S - 1 || y0 < G || y1 > H - G;
+        if (lp.wait_seq && reads_ghosts) wait_neighbors(D, lp.wait_seq, lane);
+
+        // per-lane constants
+        const bool owned_lane = lane >= 1 && lane <= kValidLanes;
+        uint32_t keep[kWL];
+#pragma unroll
+        for (int j = 0; j < kWL; ++j) {
+            const int i = vi + j;
+            uint32_t kmask = (owned_lane && i >= 0 && i < nw) ? 0xffffffffu : 0u;
+            if (rem) {
+                if (i == nwf) kmask &= rem >= 32 ? 0xffffffffu : ((1u << rem) - 1u);
+                if (i == nwf + 1) kmask &= rem > 32 ? ((1u << (rem - 32)) - 1u) : 0u;
+            }
+            keep[j] = kmask;
+        }
+        const bool store_all = (keep[0] & keep[1]) == 0xffffffffu;
+        const bool store_any = (keep[0] | keep[1]) != 0u;
+        // load mode: 1 = plain vector load, 2 = composed tail (partial word + shifted ghost), 0 = none
+        int mode;
+        if (rem == 0) mode = (vi >= -GOL_GHOST_WORDS32 && vi + kWL <= nw + GOL_GHOST_WORDS32) ? 1 : 0;
+        else mode = (vi >= -GOL_GHOST_WORDS32 && vi + kWL <= nwf) ? 1 : (vi < nwf + 4 && vi + kWL > nwf ? 2 : 0);
+
+        auto load_row = [&](int y, uint32_t(&w)[kWL]) {
+            const uint32_t *rowp = in + (int64_t)(y + G) * pitch + GOL_GHOST_WORDS32;
+            if (mode == 1) {
+                const uint2 v = *reinterpret_cast<const uint2 *>(rowp + vi);
+                w[0] = v.x; w[1] = v.y;
+            } else if (mode == 2) {
+#pragma unroll
+                for (int j = 0; j < kWL; ++j) {
+                    const int i = vi + j;
+                    uint32_t v = 0;
+                    if (i < nwf) v = rowp[i];
+                    else if (i < nwf + 4) v = (i < nw ? rowp[i] : 0u) | rowp[nw + (i - nwf)];
+                    w[j] = v;
+                }
+            } else {
+                w[0] = 0; w[1] = 0;
+            }
+        };
+
+        uint32_t h0[K][2][kWL], h1[K][2][kWL], ctr[K][kWL];
+#pragma unroll
+        for (int t = 0; t < K; ++t)
+#pragma unroll
+            for (int j = 0; j < kWL; ++j) {
+                h0[t][0][j] = h0[t][1][j] = h1[t][0][j] = h1[t][1][j] = 0;
+                ctr[t][j] = 0;
+            }
+        uint32_t acc_alive = 0, acc_diff = 0;
+
+        const int rbeg = y0 - K, rend = y1 + K;  // level-0 rows consumed: [rbeg, rend)
+        uint32_t cur[kWL], nxt_row[kWL];
+        load_row(rbeg, nxt_row);
+
+        auto step = [&](int r, auto par_tag) {
+            constexpr int PAR = decltype(par_tag)::value;
+#pragma unroll
+            for (int j = 0; j < kWL; ++j) cur[j] = nxt_row[j];
+            load_row(min(r + 1, rend - 1), nxt_row);  // prefetch
+#pragma unroll
+            for (int t = 0; t < K; ++t) {
+                // cur = row (r - t) of generation base+t
+                const uint32_t left = __shfl_up_sync(0xffffffffu, cur[kWL - 1], 1);
+                const uint32_t right = __shfl_down_sync(0xffffffffu, cur[0], 1);
+                uint32_t nw_[kWL];
+#pragma unroll
+                for (int j = 0; j < kWL; ++j) {
+                    const uint32_t pw = j ? cur[j - 1] : left;
+                    const uint32_t nx = j < kWL - 1 ? cur[j + 1] : right;
+                    const uint32_t L = __funnelshift_l(pw, cur[j], 1);
+                    const uint32_t R = __funnelshift_r(cur[j], nx, 1);
+                    const uint32_t s0 = xor3(L, cur[j], R);
+                    const uint32_t s1 = maj3(L, cur[j], R);
+                    // rows r-t-2 (slot PAR), r-t-1 (slot PAR^1, centre ctr[t]) and r-t (s0,s1)
+                    nw_[j] = life_rule(h0[t][PAR][j], h1[t][PAR][j], h0[t][PAR ^ 1][j], h1[t][PAR ^ 1][j],
+                                       s0, s1, ctr[t][j]);
+                    h0[t][PAR][j] = s0;
+                    h1[t][PAR][j] = s1;
+                    if (FLAGS && t == K - 1 && r >= y0 + K) {
+                        acc_alive |= nw_[j] & keep[j];
+                        acc_diff |= (ctr[t][j] ^ nw_[j]) & keep[j];
+                    }
+                    ctr[t][j] = cur[j];
+                }
+#pragma unroll
+                for (int j = 0; j < kWL; ++j) cur[j] = nw_[j];
+            }
+            // cur = row (r - K) of generation base+K
+            const int yo = r - K;
+            if (yo >= y0 && store_any) {
+                uint32_t *orow = out + (int64_t)(yo + G) * pitch + GOL_GHOST_WORDS32 + vi;
+                if (store_all) {
+                    *reinterpret_cast<uint2 *>(orow) = make_uint2(cur[0], cur[1]);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < kWL; ++j)
+                        if (keep[j]) orow[j] = cur[j] & keep[j];
+                }
+            }
+        };
+
+        int r = rbeg;
+        for (; r + 1 < rend; r += 2) {
+            step(r, std::integral_constant<int, 0>{});
+            step(r + 1, std::integral_constant<int, 1>{});
+        }
+        if (r < rend) step(r, std::integral_constant<int, 0>{});
+
+        if (FLAGS) {
+            const bool a = __any_sync(0xffffffffu, acc_alive != 0);
+            const bool d = __any_sync(0xffffffffu, acc_diff != 0);
+            if (lane == 0) {
+                if (a) atomicOr(&D.scratch->alive, 1u);
+                if (d) atomicOr(&D.scratch->diff, 1u);
+            }
+        }
+        __syncwarp();
+        if (border) push_borders(D, lp.out_idx, strip, y0, y1, lane);
+        if (need_done) __threadfence_system();
+    }
+    if (need_done) finish_domain(D, lp);
+}
+
+// ------------------------------------------------------------- halo kernel
+__global__ void __launch_bounds__(kWarps * 32) halo_push_kernel(const GolDomainDev *__restrict__ doms,
+                                                                const GolLaunch lp)
+{
+    const int dom_id = blockIdx.x / lp.ctas_per_domain;
+    const int cta = blockIdx.x - dom_id * lp.ctas_per_domain;
+    const GolDomainDev &D = doms[dom_id];
+    const int lane = threadIdx.x & 31;
+    const int item = cta * kWarps + (threadIdx.x >> 5);
+    const int S = D.strips;
+    const int strip = item % S, chunk = item / S;
+    const int y0 = chunk * lp.chunk_rows;
+    const int y1 = min(D.H, y0 + lp.chunk_rows);
+    if (chunk < lp.chunks && y0 < D.H) {
+        const bool border = strip == 0 || strip == S - 1 || y0 < G || y1 > D.H - G;
+        if (border) push_borders(D, lp.out_idx, strip, y0, y1, lane);
+        __threadfence_system();
+    }
+    finish_domain(D, lp);
+}
+
+// ------------------------------------------------------------- alive scan
+// empty() of the current generation (S:103-116, C:55-81) with the same record protocol.
+__global__ void __launch_bounds__(kWarps * 32) scan_alive_kernel(const GolDomainDev *__restrict__ doms,
+                                                                 const GolLaunch lp)
+{
+    const int dom_id = blockIdx.x / lp.ctas_per_domain;
+    const int cta = blockIdx.x - dom_id * lp.ctas_per_domain;
+    const GolDomainDev &D = doms[dom_id];
+    const int lane = threadIdx.x & 31;
+    const int item = cta * kWarps + (threadIdx.x >> 5);
+    const int S = D.strips;
+    const int strip = item % S, chunk = item / S;
+    const int y0 = chunk * lp.chunk_rows;
+    const int y1 = min(D.H, y0 + lp.chunk_rows);
+    if (chunk < lp.chunks && y0 < D.H) {
+        const int lo = strip_origin(strip, S, D.nw32), hi = min(D.nw32, lo + kVW);
+        const uint32_t *src = D.buf[lp.in_idx];
+        uint32_t acc = 0;
+        for (int y = y0; y < y1; ++y) {
+            const uint32_t *s = src + (int64_t)(y + G) * D.pitch32 + GOL_GHOST_WORDS32;
+            for (int i = lo + lane; i < hi; i += 32) acc |= s[i];
+        }
+        if (__any_sync(0xffffffffu, acc != 0) && lane == 0) atomicOr(&D.scratch->alive, 1u);
+    }
+    finish_domain(D, lp);
+}
+
+// ------------------------------------------------- flag all-reduce (gather)
+// One warp: waits until every domain's record for `seq` is in this process's table, ORs them.
+__global__ void gather_flags_kernel(const unsigned long long *table, int num_domains, uint32_t seq,
+                                    unsigned long long *result, unsigned int *error)
+{
+    unsigned long long acc = 0;
+    for (int i = threadIdx.x; i < num_domains; i += blockDim.x) {
+        const unsigned long long *p = table + i;
+        long long t0 = clock64();
+        unsigned long long v;
+        while ((uint32_t)((v = ld_acquire_sys64(p)) >> 32) != seq) {
+            if (clock64() - t0 > (1ll << 34)) {
+                atomicOr(error, 2u);
+                break;
+            }
+            __nanosleep(128);
+        }
+        acc |= v & 3ull;
+    }
+    for (int o = 16; o; o >>= 1) acc |= __shfl_xor_sync(0xffffffffu, acc, o);
+    __shared__ unsigned long long sh[32];
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long r = 0;
+        for (int i = 0; i < (int)(blockDim.x + 31) / 32; ++i) r |= sh[i];
+        *result = ((unsigned long long)seq << 32) | r;
+    }
+}
+
+// ------------------------------------------------ dense <-> padded copies
+__global__ void dense_to_padded_kernel(const uint64_t *__restrict__ dense, int64_t dense_pitch_q, int64_t qx0,
+                                       uint32_t *__restrict__ pad, int H, int nq, int rem, int pitch32)
+{
+    const int q = blockIdx.y * blockDim.x + threadIdx.x;
+    const int y = blockIdx.x;
+    if (q >= nq || y >= H) return;
+    uint64_t v = dense[(int64_t)y * dense_pitch_q + qx0 + q];
+    if (rem && q == nq - 1) v &= (1ull << rem) - 1ull;
+    uint64_t *row = reinterpret_cast<uint64_t *>(pad + (int64_t)(y + G) * pitch32 + GOL_GHOST_WORDS32);
+    row[q] = v;
+}
+__global__ void padded_to_dense_kernel(const uint32_t *__restrict__ pad, int H, int nq, int rem, int pitch32,
+                                       uint64_t *__restrict__ dense, int64_t dense_pitch_q, int64_t qx0)
+{
+    const int q = blockIdx.y * blockDim.x + threadIdx.x;
+    const int y = blockIdx.x;
+    if (q >= nq || y >= H) return;
+    const uint64_t *row = reinterpret_cast<const uint64_t *>(pad + (int64_t)(y + G) * pitch32 + GOL_GHOST_WORDS32);
+    uint64_t v = row[q];
+    if (rem && q == nq - 1) v &= (1ull << rem) - 1ull;
+    dense[(int64_t)y * dense_pitch_q + qx0 + q] = v;
+}
+
+template <int K, bool FLAGS>
+cudaError_t launch_strip_t(const GolDomainDev *d, int grid, const GolLaunch &lp, cudaStream_t s)
+{
+    life_strip_kernel<K, FLAGS><<<grid, kWarps * 32, 0, s>>>(d, lp);
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+int gol_strip_geometry(int nw32, int *strips)
+{
+    *strips = (int)gol_div_up(nw32, kVW);
+    return 0;
+}
+
+int gol_launch_strip(const GolDomainDev *d_doms, int ndoms, const GolLaunch &lp, int k, int want_flags,
+                     int max_items_per_domain, CUstream_st *stream)
+{
+    (void)max_items_per_domain;
+    const int grid = ndoms * lp.ctas_per_domain;
+    cudaError_t err;
+#define GOL_CASE(KK)                                                                  \
+    case KK:                                                                          \
+        err = want_flags ? launch_strip_t<KK, true>(d_doms, grid, lp, stream)         \
+                         : launch_strip_t<KK, false>(d_doms, grid, lp, stream);       \
+        break;
+    switch (k) {
+        GOL_CASE(1)
+        GOL_CASE(2)
+        GOL_CASE(4)
+        GOL_CASE(8)
+        GOL_CASE(16)
+    default:
+        GOL_FAIL("unsupported temporal depth k=%d", k);
+    }
+#undef GOL_CASE
+    if (err != cudaSuccess) GOL_FAIL("life_strip_kernel<k=%d> launch failed: %s", k, cudaGetErrorString(err));
+    return 0;
+}
+
+int gol_launch_halo(const GolDomainDev *d_doms, int ndoms, const GolLaunch &lp, int max_rows,
+                    CUstream_st *stream)
+{
+    (void)max_rows;
+    halo_push_kernel<<<ndoms * lp.ctas_per_domain, kWarps * 32, 0, stream>>>(d_doms, lp);
+    cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess) GOL_FAIL("halo_push_kernel launch failed: %s", cudaGetErrorString(err));
+    return 0;
+}
+
+int gol_launch_scan_alive(const GolDomainDev *d_doms, int ndoms, const GolLaunch &lp, CUstream_st *stream)
+{
+    scan_alive_kernel<<<ndoms * lp.ctas_per_domain, kWarps * 32, 0, stream>>>(d_doms, lp);
+    cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess) GOL_FAIL("scan_alive_kernel launch failed: %s", cudaGetErrorString(err));
+    return 0;
+}
+
+int gol_launch_gather(unsigned long long *rec_table, int slot, int num_domains, uint32_t seq,
+                      unsigned long long *d_result, unsigned int *d_error, CUstream_st *stream)
+{
+    gather_flags_kernel<<<1, 64, 0, stream>>>(rec_table + (int64_t)slot * num_domains, num_domains, seq,
+                                              d_result, d_error);
+    cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess) GOL_FAIL("gather_flags_kernel launch failed: %s", cudaGetErrorString(err));
+    return 0;
+}
+
+int gol_launch_dense_to_padded(const uint64_t *d_dense, int64_t dense_pitch_q, int64_t qx0, uint32_t *d_pad,
+                               const gol_layout &L, CUstream_st *stream)
+{
+    dim3 grid((unsigned)L.height, (unsigned)gol_div_up(L.nq, 128));
+    dense_to_padded_kernel<<<grid, 128, 0, stream>>>(d_dense, dense_pitch_q, qx0, d_pad, (int)L.height, L.nq,
+                                                     L.rem, L.pitch32);
+    cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess) GOL_FAIL("dense_to_padded launch failed: %s", cudaGetErrorString(err));
+    return 0;
+}
+
+int gol_launch_padded_to_dense(const uint32_t *d_pad, const gol_layout &L, uint64_t *d_dense,
+                               int64_t dense_pitch_q, int64_t qx0, int, CUstream_st *stream)
+{
+    dim3 grid((unsigned)L.height, (unsigned)gol_div_up(L.nq, 128));
+    padded_to_dense_kernel<<<grid, 128, 0, stream>>>(d_pad, (int)L.height, L.nq, L.rem, L.pitch32, d_dense,
+                                                     dense_pitch_q, qx0);
+    cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess) GOL_FAIL("padded_to_dense launch failed: %s", cudaGetErrorString(err));
+    return 0;
+}

@@ -1,0 +1,2 @@
+"""Parallel layer: topology / decomposition, launch helpers and the NCCL halo baseline."""
+from .topology import DIRECTIONS, OPPOSITE, Topology, auto_grid  # noqa: F401

@@ -1,0 +1,68 @@
+"""Periodic R x C process topology and block decomposition (pure Python mirror of the engine).
+
+Replaces MPI_Cart_create / MPI_Cart_coords / MPI_Cart_rank with periods {1,1}
+(src/game_mpi_collective.c:120-137, 225-275 of the reference) for any R x C, not just
+perfect squares, and with "north" meaning the row above (the reference wires north/south
+backwards for more than 2 process rows, defect D1 in SURVEY.md).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+# direction order shared with the native engine: N, S, W, E, NW, NE, SW, SE
+DIRECTIONS = ("N", "S", "W", "E", "NW", "NE", "SW", "SE")
+_DY = (-1, 1, 0, 0, -1, -1, 1, 1)
+_DX = (0, 0, -1, 1, -1, 1, -1, 1)
+OPPOSITE = (1, 0, 3, 2, 7, 6, 5, 4)
+
+
+def auto_grid(n: int) -> tuple[int, int]:
+    """Near-square factorisation R x C = n with R <= C (8 -> 2x4, 4 -> 2x2, 2 -> 1x2)."""
+    best = 1
+    i = 1
+    while i * i <= n:
+        if n % i == 0:
+            best = i
+        i += 1
+    return best, n // best
+
+
+@dataclass(frozen=True)
+class Topology:
+    width: int
+    height: int
+    rows: int
+    cols: int
+
+    @property
+    def size(self) -> int:
+        return self.rows * self.cols
+
+    def coords(self, gid: int) -> tuple[int, int]:
+        return gid // self.cols, gid % self.cols
+
+    def gid(self, r: int, c: int) -> int:
+        return (r % self.rows) * self.cols + (c % self.cols)
+
+    def neighbors(self, gid: int) -> list[int]:
+        r, c = self.coords(gid)
+        return [self.gid(r + dy, c + dx) for dy, dx in zip(_DY, _DX)]
+
+    def col_bounds(self) -> list[int]:
+        """Columns are split at 64-cell word boundaries; the last column takes the remainder."""
+        nq = (self.width + 63) // 64
+        b = [min(self.width, (nq * c // self.cols) * 64) for c in range(self.cols + 1)]
+        b[-1] = self.width
+        return b
+
+    def row_bounds(self) -> list[int]:
+        return [self.height * r // self.rows for r in range(self.rows + 1)]
+
+    def extent(self, gid: int) -> tuple[int, int, int, int]:
+        r, c = self.coords(gid)
+        xb, yb = self.col_bounds(), self.row_bounds()
+        return xb[c], yb[r], xb[c + 1] - xb[c], yb[r + 1] - yb[r]
+
+    def owner(self, gid: int, world: int) -> int:
+        """Domains are dealt to processes in contiguous blocks."""
+        return gid // (self.size // world)

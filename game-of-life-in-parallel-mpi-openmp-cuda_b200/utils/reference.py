@@ -1,0 +1,67 @@
+"""Builds and runs the UNMODIFIED reference programs as oracle / baseline.
+
+Sources are copied verbatim from the read-only reference checkout into ``baseline/_ref/src``
+(git-ignored, but it travels to the GPU box with the snapshot) and compiled there with the
+reference's own flags (``Makefile:10-13, 27-28`` of the reference).  Nothing from these
+sources is used by the product.
+"""
+from __future__ import annotations
+
+import os
+import re
+import shutil
+import subprocess
+
+from .._native import REPO_ROOT
+
+REF_SRC = os.environ.get("GOL_REFERENCE_DIR", "/root/reference")
+REF_DIR = os.path.join(REPO_ROOT, "baseline", "_ref")
+
+
+def stage_sources() -> str | None:
+    """Copy the reference tree into baseline/_ref (idempotent); None if it is not reachable."""
+    dst = os.path.join(REF_DIR, "src")
+    if os.path.exists(os.path.join(dst, "game.c")):
+        return REF_DIR
+    if not os.path.exists(os.path.join(REF_SRC, "src", "game.c")):
+        return None
+    os.makedirs(REF_DIR, exist_ok=True)
+    for sub in ("src", "include"):
+        shutil.copytree(os.path.join(REF_SRC, sub), os.path.join(REF_DIR, sub), dirs_exist_ok=True)
+    for f in ("Makefile", "generate.sh", "README.md"):
+        shutil.copy(os.path.join(REF_SRC, f), os.path.join(REF_DIR, f))
+    return REF_DIR
+
+
+def build_serial() -> str | None:
+    """gcc -std=c99 -Wall -O3 src/game.c (the reference's `make game`)."""
+    if stage_sources() is None:
+        return None
+    exe = os.path.join(REF_DIR, "game_serial")
+    if not os.path.exists(exe):
+        subprocess.run(["gcc", "-std=c99", "-Wall", "-O3", "src/game.c", "-o", exe], cwd=REF_DIR, check=True,
+                       stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    return exe
+
+
+def build_cuda(arch_native: bool = False) -> str | None:
+    """`nvcc src/game_cuda.cu` as shipped (PTX-JIT on B200) or with -O3 -arch=sm_100."""
+    if stage_sources() is None or shutil.which("nvcc") is None:
+        return None
+    exe = os.path.join(REF_DIR, "game_cuda_sm100" if arch_native else "game_cuda_asshipped")
+    if not os.path.exists(exe):
+        cmd = ["nvcc"] + (["-O3", "-arch=sm_100"] if arch_native else []) + ["src/game_cuda.cu", "-o", exe]
+        subprocess.run(cmd, cwd=REF_DIR, check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    return exe
+
+
+def run_program(exe: str, width: int, height: int, input_path: str, workdir: str, output_name: str,
+                timeout: float | None = None):
+    """Runs `exe W H input` in workdir; returns (generations, execution_ms, output bytes, stdout)."""
+    p = subprocess.run([exe, str(width), str(height), os.path.abspath(input_path)], cwd=workdir,
+                       capture_output=True, text=True, timeout=timeout, check=True)
+    gens = re.search(r"Generations:\s+(\d+)", p.stdout)
+    ms = re.search(r"Execution time:\s+([0-9.]+)", p.stdout)
+    with open(os.path.join(workdir, output_name), "rb") as f:
+        out = f.read()
+    return (int(gens.group(1)) if gens else None, float(ms.group(1)) if ms else None, out, p.stdout)
