@@ -124,7 +124,17 @@ int run_rank(const Options &opt, int rank, int nproc, Shared *sh)
     cfg.batch_gens = opt.batch;
     cfg.flags = opt.generic ? GOL_FLAG_FORCE_GENERIC : 0;
     gol_engine *eng = nullptr;
-    if (gol_engine_create(&cfg, &eng)) die(sh, "engine");
+    if (gol_engine_create(&cfg, &eng)) {
+        // a decomposition finer than the strip kernel's minimum domain: fall back to one domain
+        // (only possible when all domains live in this process)
+        if (nproc == 1 && cfg.grid_rows * cfg.grid_cols > 1) {
+            fprintf(stderr, "note: %s; running as a single domain\n", gol_last_error());
+            cfg.grid_rows = cfg.grid_cols = 1;
+            if (gol_engine_create(&cfg, &eng)) die(sh, "engine");
+        } else {
+            die(sh, "engine");
+        }
+    }
     if (nproc > 1) {
         if (gol_engine_ipc_blob_size(eng) > sizeof sh->blobs[0]) {
             fprintf(stderr, "ipc blob too large\n");

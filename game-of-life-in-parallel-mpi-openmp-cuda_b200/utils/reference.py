@@ -30,6 +30,10 @@ def stage_sources() -> str | None:
         shutil.copytree(os.path.join(REF_SRC, sub), os.path.join(REF_DIR, sub), dirs_exist_ok=True)
     for f in ("Makefile", "generate.sh", "README.md"):
         shutil.copy(os.path.join(REF_SRC, f), os.path.join(REF_DIR, f))
+    for root, dirs, files in os.walk(REF_DIR):   # the checkout is read-only; the copy must not be
+        for name in dirs + files:
+            path = os.path.join(root, name)
+            os.chmod(path, os.stat(path).st_mode | 0o200)
     return REF_DIR
 
 

@@ -1,0 +1,193 @@
+"""GPU tests of the engine: strip kernel (all temporal depths, ragged widths, multi-strip),
+multi-domain decomposition emulated as one launch, exact early-exit semantics, file I/O."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def make(w, h, **kw):
+    import gol_b200
+    return gol_b200.GameOfLife(w, h, device=0, **kw)
+
+
+def check_steps(w, h, schedule, seed=1, **kw):
+    from gol_b200.ops import cpu
+    start = cpu.random_grid(w, h, seed)
+    life = make(w, h, **kw)
+    life.load_packed(start)
+    want = start
+    for n in schedule:
+        life.step(n)
+        want = cpu.step(want, w, n)
+        got = life.packed_numpy()
+        assert np.array_equal(got, want), f"{w}x{h} {kw} mismatch after +{n}"
+    life.close()
+
+
+@pytest.mark.parametrize("w,h", [(128, 16), (192, 40), (840, 840), (1000, 70), (129, 33), (191, 20), (200, 64),
+                                 (2048, 64), (1984, 48), (3900, 50), (4096, 300), (7000, 37)])
+def test_strip_kernel_matches_cpu(cuda_device, w, h):
+    check_steps(w, h, [1, 2, 3, 5, 8, 16, 23])
+
+
+@pytest.mark.parametrize("k", [1, 2, 4, 8, 16])
+def test_temporal_depths(cuda_device, k):
+    check_steps(1100, 200, [k, 3 * k + 1, 37], k_max=k)
+
+
+@pytest.mark.parametrize("grid", [(1, 2), (2, 1), (2, 2), (2, 4), (1, 8), (8, 1), (3, 3), (4, 2)])
+def test_multi_domain_emulated(cuda_device, grid):
+    # all R*C domains live in this process and are advanced by ONE launch per epoch; borders
+    # travel through the same fused push that writes peer memory on a multi-GPU job
+    check_steps(2240, 384, [1, 4, 7, 16, 30], grid=grid)
+    check_steps(1500, 210, [5, 11], grid=grid, seed=3)
+
+
+def test_glider_crosses_every_seam(cuda_device):
+    from gol_b200.ops import cpu
+    from gol_b200.utils import patterns
+    w, h = 512, 128
+    cells = patterns.grid_with(w, h, ("glider", w - 2, h - 2), ("glider", 254, 62), ("glider", 100, 10))
+    start = cpu.pack(cells)
+    for grid in [(1, 1), (2, 2), (2, 4)]:
+        life = make(w, h, grid=grid)
+        life.load_packed(start)
+        life.step(4 * 70)
+        assert np.array_equal(life.packed_numpy(), cpu.step(start, w, 4 * 70))
+        assert life.population() == 15
+        life.close()
+
+
+def run_both(cells, **kw):
+    from gol_b200.ops import cpu
+    h, w = cells.shape
+    start = cpu.pack(cells)
+    cfg = {k: v for k, v in kw.items() if k in ("gen_limit", "similarity_frequency")}
+    want, wres = cpu.run(start, w, **cfg)
+    life = make(w, h, **kw)
+    life.load_packed(start)
+    res = life.run()
+    got = life.packed_numpy()
+    life.close()
+    assert (res.generations, res.exit_reason) == (wres.generations, wres.exit_reason), (res, wres, kw)
+    assert np.array_equal(got, want)
+    assert res.population == wres.population
+    return res
+
+
+def test_run_semantics_fixtures(cuda_device):
+    from gol_b200.utils import patterns
+    w, h = 256, 64
+    cases = {
+        "empty": [], "cell": [("cell", 5, 5)], "block": [("block", 9, 9)], "tromino": [("tromino", 9, 9)],
+        "blinker": [("blinker", 100, 30)], "beehive": [("beehive", 200, 40)], "diag3": [("diag3", 30, 30)],
+        "pulsar": [("pulsar", 64, 20)], "rpent": [("rpentomino", 128, 32)],
+        "seam": [("block", 255, 63), ("tromino", 126, 31)],
+    }
+    for name, stamps in cases.items():
+        cells = patterns.grid_with(w, h, *stamps)
+        for kw in ({}, {"grid": (2, 2)}, {"k_max": 8, "batch_gens": 24}, {"similarity_frequency": 0, "gen_limit": 50},
+                   {"similarity_frequency": 5}, {"gen_limit": 7}):
+            run_both(cells, **kw)
+
+
+def test_run_stabilising_at_every_residue(cuda_device):
+    # a tromino placed after d blinker-free generations of delay: block forms at generation 1;
+    # shifting the similarity frequency walks the exit through every residue class
+    from gol_b200.utils import patterns
+    cells = patterns.grid_with(192, 32, ("tromino", 50, 10), ("diag3", 120, 12))
+    for freq in (1, 2, 3, 4, 5, 7):
+        for limit in (1, 2, 3, 4, 6, 1000):
+            run_both(cells, similarity_frequency=freq, gen_limit=limit)
+
+
+def test_run_random_sparse_grids(cuda_device):
+    # sparse random grids die or stabilise at assorted generations
+    rng = np.random.default_rng(5)
+    for i in range(6):
+        cells = (rng.random((48, 160)) < 0.04 + 0.01 * i).astype(np.uint8)
+        run_both(cells, gen_limit=300)
+        run_both(cells, gen_limit=300, grid=(1, 1), batch_gens=32, k_max=2)
+
+
+def test_generic_path_small_grids(cuda_device):
+    from gol_b200.utils import patterns
+    rng = np.random.default_rng(11)
+    for w, h in [(30, 30), (1, 1), (2, 2), (5, 3), (64, 8), (100, 10)]:
+        cells = (rng.random((h, w)) < 0.35).astype(np.uint8)
+        r = run_both(cells, gen_limit=200)
+        assert r is not None
+    life = make(30, 30)
+    assert not life.uses_fast_path
+    life.close()
+    run_both(patterns.grid_with(30, 30, ("block", 3, 3)))
+    run_both(patterns.grid_with(512, 64, ("block", 3, 3)), force_generic=True)
+
+
+def test_tensor_views(cuda_device):
+    from gol_b200.ops import cpu
+    w, h = 840, 100
+    start = cpu.random_grid(w, h, 4)
+    life = make(w, h)
+    life.load_packed(start)
+    t = life.packed()
+    assert t.dtype == torch.int64 and tuple(t.shape) == (h, 14) and t.is_cuda
+    assert np.array_equal(t.cpu().numpy().view(np.uint64), start)
+    assert np.array_equal(life.cells().cpu().numpy(), cpu.unpack(start, w))
+    life.step(3)
+    assert np.array_equal(life.packed().cpu().numpy().view(np.uint64), cpu.step(start, w, 3))
+    life.close()
+
+
+@pytest.mark.parametrize("grid", [(1, 1), (2, 2), (1, 3)])
+def test_text_file_io(cuda_device, tmp_path, grid):
+    from gol_b200.ops import cpu
+    w, h = 840, 77
+    inp, out = tmp_path / "in.txt", tmp_path / "out.txt"
+    cpu.random_text_file(str(inp), w, h, 21)
+    life = make(w, h, grid=grid)
+    life.load_file(str(inp))
+    assert np.array_equal(life.packed_numpy(), cpu.random_grid(w, h, 21))
+    life.step(5)
+    out.write_bytes(b"stale content that is longer than nothing" * 4000)
+    life.save(str(out))
+    assert out.read_bytes() == cpu.format_text(cpu.step(cpu.random_grid(w, h, 21), w, 5), w)
+    short = tmp_path / "short.txt"
+    short.write_bytes(inp.read_bytes()[: (w + 1) * 10])
+    with pytest.raises(Exception, match="too short"):
+        life.load_file(str(short))
+    garbled = bytearray(inp.read_bytes())
+    garbled[(w + 1) * 3 + 17] = ord("7")
+    (tmp_path / "bad.txt").write_bytes(bytes(garbled))
+    with pytest.raises(Exception, match="invalid byte"):
+        life.load_file(str(tmp_path / "bad.txt"))
+    life.close()
+
+
+def test_cli_matches_unmodified_reference(cuda_device, ref_serial, tmp_path):
+    from gol_b200.ops import cpu
+    from gol_b200.utils import reference
+    n = 256
+    inp = tmp_path / "in.txt"
+    cpu.random_text_file(str(inp), n, n, 33)
+    gens, _, want, _ = reference.run_program(ref_serial, n, n, str(inp), str(tmp_path), "game_output.out")
+    os.rename(tmp_path / "game_output.out", tmp_path / "ref.out")
+    exe = os.path.join(ROOT, "bin", "gol")
+    for variant, extra in [("game", []), ("cuda", []), ("collective", ["--ranks", "4"])]:
+        p = subprocess.run([exe, str(n), str(n), str(inp), "--variant", variant] + extra, cwd=tmp_path,
+                           capture_output=True, text=True, check=True)
+        assert f"Generations:\t{gens}\n" in p.stdout, p.stdout
+        assert "Execution time:\t" in p.stdout and p.stdout.rstrip().endswith("Finished")
+        assert (tmp_path / f"{variant}_output.out").read_bytes() == want
+        if variant == "collective":
+            assert p.stdout.startswith("Reading file:\t") and "Writing file:\t" in p.stdout
+    # fewer than three arguments: the C programs do nothing and print Finished (S:238-241)
+    p = subprocess.run([exe, "10"], cwd=tmp_path, capture_output=True, text=True, check=True)
+    assert p.stdout == "Finished\n"

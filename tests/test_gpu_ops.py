@@ -1,0 +1,75 @@
+"""GPU tests of the stand-alone device ops against plain PyTorch fp32 references."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def conv_oracle(cells: torch.Tensor) -> torch.Tensor:
+    """Plain PyTorch fp32 reference: circular-padded 3x3 conv + B3/S23 rule."""
+    x = cells.to(torch.float32)[None, None]
+    h, w = cells.shape
+    # explicit torus gather (works for every size >= 1, like the serial reference's wrap)
+    ys = torch.arange(h, device=cells.device)
+    xs = torch.arange(w, device=cells.device)
+    n = torch.zeros_like(x)
+    for dy in (-1, 0, 1):
+        for dx in (-1, 0, 1):
+            if dy == 0 and dx == 0:
+                continue
+            n += x[:, :, (ys + dy) % h][:, :, :, (xs + dx) % w]
+    alive = (n == 3) | ((n == 2) & (x == 1))
+    return alive[0, 0].to(torch.uint8)
+
+
+SIZES = [(1, 1), (1, 4), (4, 1), (2, 2), (3, 5), (30, 30), (63, 7), (64, 64), (65, 9), (129, 33), (1000, 17)]
+
+
+@pytest.mark.parametrize("w,h", SIZES)
+def test_step_dense_matches_conv2d(cuda_device, w, h):
+    from gol_b200.ops import dense
+    g = torch.Generator(device="cpu").manual_seed(w * 131 + h)
+    cells = (torch.rand((h, w), generator=g) < 0.4).to(torch.uint8).to(cuda_device)
+    packed = dense.pack_cells(cells)
+    assert torch.equal(dense.unpack_cells(packed, w), cells)
+    cur = cells
+    for _ in range(3):
+        flags = torch.zeros(2, dtype=torch.int32, device=cuda_device)
+        nxt = dense.step(packed, w, flags=flags)
+        want = conv_oracle(cur)
+        assert torch.equal(dense.unpack_cells(nxt, w), want)
+        assert bool(flags[0].item()) == bool(want.any().item())
+        assert bool(flags[1].item()) == (not torch.equal(want, cur))
+        packed, cur = nxt, want
+
+
+def test_flags_empty_similar(cuda_device):
+    from gol_b200.ops import dense
+    z = torch.zeros((5, 2), dtype=torch.int64, device=cuda_device)
+    assert dense.empty(z, 100) and dense.similar(z, z.clone(), 100)
+    a = z.clone()
+    a[3, 1] = 1 << 20
+    assert not dense.empty(a, 100) and not dense.similar(a, z, 100)
+    assert dense.population(a, 100) == 1
+
+
+def test_parse_format_random_match_cpu(cuda_device):
+    from gol_b200.ops import cpu, dense
+    for w, h in [(70, 13), (64, 3), (1, 1), (1025, 5)]:
+        want = cpu.random_grid(w, h, 9)
+        got = dense.random_grid(w, h, 9, device=cuda_device)
+        assert np.array_equal(got.cpu().numpy().view(np.uint64), want)
+        text = dense.format_text(got, w)
+        assert bytes(text.cpu().numpy().tobytes()) == cpu.format_text(want, w)
+        back = dense.parse_text(text, w, h)
+        assert torch.equal(back, got)
+        assert dense.population(got, w) == int(cpu.unpack(want, w).sum())
+    bad = text.clone()
+    bad[0, 3] = ord("x")
+    with pytest.raises(Exception, match="invalid byte"):
+        dense.parse_text(bad, 1025, 5)
+    bad = text.clone()
+    bad[2, 1025] = ord("0")
+    with pytest.raises(Exception, match="newline"):
+        dense.parse_text(bad, 1025, 5)
