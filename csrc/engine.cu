@@ -18,6 +18,7 @@
 
 #include <algorithm>
 #include <cerrno>
+#include <cstdlib>
 #include <fcntl.h>
 #include <sys/stat.h>
 #include <unistd.h>
@@ -90,7 +91,7 @@ struct gol_engine {
     bool own_stream = false;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     double last_ms = 0.0;
-    int kmax = 4, batch = 120;
+    int kmax = 8, batch = 128;
 };
 
 namespace {
@@ -205,7 +206,8 @@ int upload_domains(gol_engine *e)
 // chunk) against the number of independent warps.
 void geometry(const gol_engine *e, int k, GolLaunch *lp)
 {
-    const int64_t target_items = (int64_t)e->num_sms * 16 / std::max(1, e->per_proc);
+    static const int warps_per_sm = getenv("GOL_WARPS_PER_SM") ? atoi(getenv("GOL_WARPS_PER_SM")) : 16;
+    const int64_t target_items = (int64_t)e->num_sms * warps_per_sm / std::max(1, e->per_proc);
     int64_t chunks = std::max<int64_t>(1, (target_items + e->max_strips - 1) / e->max_strips);
     int64_t rows = gol_div_up(e->max_h, chunks);
     const int64_t min_rows = std::min<int64_t>(e->max_h, std::max<int64_t>(8, 6 * k));
@@ -632,7 +634,7 @@ int gol_engine_create(const gol_config *cfg_in, gol_engine **out)
                  GOL_MIN_FAST_HEIGHT);
     }
     e->fast = fast;
-    e->kmax = cfg.k_max > 0 ? cfg.k_max : 4;
+    e->kmax = cfg.k_max > 0 ? cfg.k_max : 8;
     if (e->kmax > GOL_GHOST_ROWS) e->kmax = GOL_GHOST_ROWS;
     int kk = 1;
     while (kk * 2 <= e->kmax) kk *= 2;

@@ -201,6 +201,148 @@ __device__ void finish_domain(const GolDomainDev &D, const GolLaunch &lp)
 }
 
 // ------------------------------------------------------------- strip kernel
+__device__ __forceinline__ uint2 ldg_v2(const uint32_t *p)
+{
+    uint2 v;
+    asm("ld.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ uint32_t ldg_u32(const uint32_t *p)
+{
+    uint32_t v;
+    asm("ld.global.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void stg_v2(uint32_t *p, uint32_t a, uint32_t b)
+{
+    asm volatile("st.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(a), "r"(b) : "memory");
+}
+__device__ __forceinline__ void stg_u32(uint32_t *p, uint32_t a)
+{
+    asm volatile("st.global.u32 [%0], %1;" ::"l"(p), "r"(a) : "memory");
+}
+
+struct MarchArgs {
+    const uint32_t *in;   // padded input buffer (global)
+    uint32_t *out;        // padded output buffer (global)
+    int pitch, nw, nwf, rem;
+    int vi;               // virtual word index of this lane's first word
+    int y0, y1;           // output rows [y0, y1)
+    uint32_t keep[kWL];   // per-word ownership / tail mask of this lane
+    int mode;             // 1 plain vector load, 2 composed ragged tail, 0 nothing to load
+};
+
+// One warp streams rows [y0-K, y1+K) of generation g through K register-resident levels and
+// writes rows [y0, y1) of generation g+K.  FAST: every lane does a plain vector load and a
+// (predicated) vector store - true for all strips except the ragged right edge of a row.
+template <int K, bool FLAGS, bool FAST>
+__device__ __forceinline__ void march(const MarchArgs &A, uint32_t &flag_alive, uint32_t &flag_diff)
+{
+    const int pitch = A.pitch;
+    const bool store_all = (A.keep[0] & A.keep[1]) == 0xffffffffu;
+    const bool store_any = (A.keep[0] | A.keep[1]) != 0u;
+    const int rbeg = A.y0 - K, rend = A.y1 + K;  // level-0 rows consumed: [rbeg, rend)
+    const uint32_t *pin = A.in + (int64_t)(rbeg + G) * pitch + GOL_GHOST_WORDS32;  // row being loaded
+    uint32_t *pout = A.out + (int64_t)(A.y0 + G) * pitch + GOL_GHOST_WORDS32 + A.vi;
+
+    auto load_row = [&](uint32_t(&w)[kWL]) {
+        if (FAST || A.mode == 1) {
+            const uint2 v = ldg_v2(pin + A.vi);
+            w[0] = v.x; w[1] = v.y;
+        } else if (A.mode == 2) {
+#pragma unroll
+            for (int j = 0; j < kWL; ++j) {
+                const int i = A.vi + j;
+                uint32_t v = 0;
+                if (i < A.nwf) v = ldg_u32(pin + i);
+                else if (i < A.nwf + 4) v = (i < A.nw ? ldg_u32(pin + i) : 0u) | ldg_u32(pin + A.nw + (i - A.nwf));
+                w[j] = v;
+            }
+        } else {
+            w[0] = 0; w[1] = 0;
+        }
+        pin += pitch;
+    };
+
+    uint32_t h0[K][2][kWL], h1[K][2][kWL], ctr[K][kWL];
+#pragma unroll
+    for (int t = 0; t < K; ++t)
+#pragma unroll
+        for (int j = 0; j < kWL; ++j) {
+            h0[t][0][j] = h0[t][1][j] = h1[t][0][j] = h1[t][1][j] = 0;
+            ctr[t][j] = 0;
+        }
+    uint32_t acc_a[kWL] = {0, 0}, acc_d[kWL] = {0, 0};
+
+    // two rows of prefetch in flight
+    uint32_t cur[kWL], q0[kWL], q1[kWL];
+    load_row(q0);
+    if (rbeg + 1 < rend) load_row(q1);
+    else { q1[0] = q0[0]; q1[1] = q0[1]; }
+
+    auto step = [&](int r, auto par_tag) {
+        constexpr int PAR = decltype(par_tag)::value;
+#pragma unroll
+        for (int j = 0; j < kWL; ++j) { cur[j] = q0[j]; q0[j] = q1[j]; }
+        if (r + 2 < rend) load_row(q1);
+#pragma unroll
+        for (int t = 0; t < K; ++t) {
+            // cur = row (r - t) of generation g+t
+            const uint32_t left = __shfl_up_sync(0xffffffffu, cur[kWL - 1], 1);
+            const uint32_t right = __shfl_down_sync(0xffffffffu, cur[0], 1);
+            uint32_t nw_[kWL];
+#pragma unroll
+            for (int j = 0; j < kWL; ++j) {
+                const uint32_t pw = j ? cur[j - 1] : left;
+                const uint32_t nx = j < kWL - 1 ? cur[j + 1] : right;
+                const uint32_t L = __funnelshift_l(pw, cur[j], 1);
+                const uint32_t R = __funnelshift_r(cur[j], nx, 1);
+                const uint32_t s0 = xor3(L, cur[j], R);
+                const uint32_t s1 = maj3(L, cur[j], R);
+                // rows r-t-2 (slot PAR), r-t-1 (slot PAR^1, centre ctr[t]) and r-t (s0,s1)
+                nw_[j] = life_rule(h0[t][PAR][j], h1[t][PAR][j], h0[t][PAR ^ 1][j], h1[t][PAR ^ 1][j], s0, s1,
+                                   ctr[t][j]);
+                h0[t][PAR][j] = s0;
+                h1[t][PAR][j] = s1;
+                if (FLAGS && t == K - 1 && r >= A.y0 + K) {
+                    acc_a[j] |= nw_[j];
+                    acc_d[j] = lop3<0xF6>(acc_d[j], ctr[t][j], nw_[j]);  // acc | (old ^ new)
+                }
+                ctr[t][j] = cur[j];
+            }
+#pragma unroll
+            for (int j = 0; j < kWL; ++j) cur[j] = nw_[j];
+        }
+        // cur = row (r - K) of generation g+K
+        if (r - K >= A.y0) {
+            if (FAST) {
+                if (store_all) stg_v2(pout, cur[0], cur[1]);
+            } else if (store_any) {
+                if (store_all) {
+                    stg_v2(pout, cur[0], cur[1]);
+                } else {
+#pragma unroll
+                    for (int j = 0; j < kWL; ++j)
+                        if (A.keep[j]) stg_u32(pout + j, cur[j] & A.keep[j]);
+                }
+            }
+            pout += pitch;
+        }
+    };
+
+    int r = rbeg;
+    for (; r + 1 < rend; r += 2) {
+        step(r, std::integral_constant<int, 0>{});
+        step(r + 1, std::integral_constant<int, 1>{});
+    }
+    if (r < rend) step(r, std::integral_constant<int, 0>{});
+
+    if (FLAGS) {
+        flag_alive = (acc_a[0] & A.keep[0]) | (acc_a[1] & A.keep[1]);
+        flag_diff = (acc_d[0] & A.keep[0]) | (acc_d[1] & A.keep[1]);
+    }
+}
+
 template <int K, bool FLAGS>
 __global__ void __launch_bounds__(kWarps * 32) life_strip_kernel(const GolDomainDev *__restrict__ doms,
                                                                  const GolLaunch lp)
@@ -218,124 +360,41 @@ __global__ void __launch_bounds__(kWarps * 32) life_strip_kernel(const GolDomain
     const bool need_done = lp.signal || lp.rec_slot >= 0;
 
     if (chunk < lp.chunks && y0 < H) {
-        const int nw = D.nw32, nwf = D.nwf32, rem = D.rem, pitch = D.pitch32;
-        const uint32_t *__restrict__ in = D.buf[lp.in_idx];
-        uint32_t *__restrict__ out = D.buf[lp.out_idx];
-        const int vi = strip_origin(strip, S, nw) - kWL + lane * kWL;  // virtual index of this lane's first word
+        MarchArgs A;
+        A.nw = D.nw32; A.nwf = D.nwf32; A.rem = D.rem; A.pitch = D.pitch32;
+        A.in = reinterpret_cast<const uint32_t *>(__cvta_generic_to_global(D.buf[lp.in_idx]));
+        A.out = reinterpret_cast<uint32_t *>(__cvta_generic_to_global(D.buf[lp.out_idx]));
+        A.vi = strip_origin(strip, S, A.nw) - kWL + lane * kWL;
+        A.y0 = y0; A.y1 = y1;
         const bool reads_ghosts = strip == 0 || strip == S - 1 || y0 - K < 0 || y1 + K > H;
         const bool border = strip == 0 || strip == S - 1 || y0 < G || y1 > H - G;
         if (lp.wait_seq && reads_ghosts) wait_neighbors(D, lp.wait_seq, lane);
 
         // per-lane constants
         const bool owned_lane = lane >= 1 && lane <= kValidLanes;
-        uint32_t keep[kWL];
 #pragma unroll
         for (int j = 0; j < kWL; ++j) {
-            const int i = vi + j;
-            uint32_t kmask = (owned_lane && i >= 0 && i < nw) ? 0xffffffffu : 0u;
-            if (rem) {
-                if (i == nwf) kmask &= rem >= 32 ? 0xffffffffu : ((1u << rem) - 1u);
-                if (i == nwf + 1) kmask &= rem > 32 ? ((1u << (rem - 32)) - 1u) : 0u;
+            const int i = A.vi + j;
+            uint32_t kmask = (owned_lane && i >= 0 && i < A.nw) ? 0xffffffffu : 0u;
+            if (A.rem) {
+                if (i == A.nwf) kmask &= A.rem >= 32 ? 0xffffffffu : ((1u << A.rem) - 1u);
+                if (i == A.nwf + 1) kmask &= A.rem > 32 ? ((1u << (A.rem - 32)) - 1u) : 0u;
             }
-            keep[j] = kmask;
+            A.keep[j] = kmask;
         }
-        const bool store_all = (keep[0] & keep[1]) == 0xffffffffu;
-        const bool store_any = (keep[0] | keep[1]) != 0u;
         // load mode: 1 = plain vector load, 2 = composed tail (partial word + shifted ghost), 0 = none
-        int mode;
-        if (rem == 0) mode = (vi >= -GOL_GHOST_WORDS32 && vi + kWL <= nw + GOL_GHOST_WORDS32) ? 1 : 0;
-        else mode = (vi >= -GOL_GHOST_WORDS32 && vi + kWL <= nwf) ? 1 : (vi < nwf + 4 && vi + kWL > nwf ? 2 : 0);
+        if (A.rem == 0) A.mode = (A.vi >= -GOL_GHOST_WORDS32 && A.vi + kWL <= A.nw + GOL_GHOST_WORDS32) ? 1 : 0;
+        else A.mode = (A.vi >= -GOL_GHOST_WORDS32 && A.vi + kWL <= A.nwf) ? 1 : (A.vi < A.nwf + 4 && A.vi + kWL > A.nwf ? 2 : 0);
+        const bool all_or_none = (A.keep[0] & A.keep[1]) == 0xffffffffu || (A.keep[0] | A.keep[1]) == 0u;
+        const bool fast = __all_sync(0xffffffffu, A.mode == 1 && all_or_none);
 
-        auto load_row = [&](int y, uint32_t(&w)[kWL]) {
-            const uint32_t *rowp = in + (int64_t)(y + G) * pitch + GOL_GHOST_WORDS32;
-            if (mode == 1) {
-                const uint2 v = *reinterpret_cast<const uint2 *>(rowp + vi);
-                w[0] = v.x; w[1] = v.y;
-            } else if (mode == 2) {
-#pragma unroll
-                for (int j = 0; j < kWL; ++j) {
-                    const int i = vi + j;
-                    uint32_t v = 0;
-                    if (i < nwf) v = rowp[i];
-                    else if (i < nwf + 4) v = (i < nw ? rowp[i] : 0u) | rowp[nw + (i - nwf)];
-                    w[j] = v;
-                }
-            } else {
-                w[0] = 0; w[1] = 0;
-            }
-        };
-
-        uint32_t h0[K][2][kWL], h1[K][2][kWL], ctr[K][kWL];
-#pragma unroll
-        for (int t = 0; t < K; ++t)
-#pragma unroll
-            for (int j = 0; j < kWL; ++j) {
-                h0[t][0][j] = h0[t][1][j] = h1[t][0][j] = h1[t][1][j] = 0;
-                ctr[t][j] = 0;
-            }
-        uint32_t acc_alive = 0, acc_diff = 0;
-
-        const int rbeg = y0 - K, rend = y1 + K;  // level-0 rows consumed: [rbeg, rend)
-        uint32_t cur[kWL], nxt_row[kWL];
-        load_row(rbeg, nxt_row);
-
-        auto step = [&](int r, auto par_tag) {
-            constexpr int PAR = decltype(par_tag)::value;
-#pragma unroll
-            for (int j = 0; j < kWL; ++j) cur[j] = nxt_row[j];
-            load_row(min(r + 1, rend - 1), nxt_row);  // prefetch
-#pragma unroll
-            for (int t = 0; t < K; ++t) {
-                // cur = row (r - t) of generation base+t
-                const uint32_t left = __shfl_up_sync(0xffffffffu, cur[kWL - 1], 1);
-                const uint32_t right = __shfl_down_sync(0xffffffffu, cur[0], 1);
-                uint32_t nw_[kWL];
-#pragma unroll
-                for (int j = 0; j < kWL; ++j) {
-                    const uint32_t pw = j ? cur[j - 1] : left;
-                    const uint32_t nx = j < kWL - 1 ? cur[j + 1] : right;
-                    const uint32_t L = __funnelshift_l(pw, cur[j], 1);
-                    const uint32_t R = __funnelshift_r(cur[j], nx, 1);
-                    const uint32_t s0 = xor3(L, cur[j], R);
-                    const uint32_t s1 = maj3(L, cur[j], R);
-                    // rows r-t-2 (slot PAR), r-t-1 (slot PAR^1, centre ctr[t]) and r-t (s0,s1)
-                    nw_[j] = life_rule(h0[t][PAR][j], h1[t][PAR][j], h0[t][PAR ^ 1][j], h1[t][PAR ^ 1][j],
-                                       s0, s1, ctr[t][j]);
-                    h0[t][PAR][j] = s0;
-                    h1[t][PAR][j] = s1;
-                    if (FLAGS && t == K - 1 && r >= y0 + K) {
-                        acc_alive |= nw_[j] & keep[j];
-                        acc_diff |= (ctr[t][j] ^ nw_[j]) & keep[j];
-                    }
-                    ctr[t][j] = cur[j];
-                }
-#pragma unroll
-                for (int j = 0; j < kWL; ++j) cur[j] = nw_[j];
-            }
-            // cur = row (r - K) of generation base+K
-            const int yo = r - K;
-            if (yo >= y0 && store_any) {
-                uint32_t *orow = out + (int64_t)(yo + G) * pitch + GOL_GHOST_WORDS32 + vi;
-                if (store_all) {
-                    *reinterpret_cast<uint2 *>(orow) = make_uint2(cur[0], cur[1]);
-                } else {
-#pragma unroll
-                    for (int j = 0; j < kWL; ++j)
-                        if (keep[j]) orow[j] = cur[j] & keep[j];
-                }
-            }
-        };
-
-        int r = rbeg;
-        for (; r + 1 < rend; r += 2) {
-            step(r, std::integral_constant<int, 0>{});
-            step(r + 1, std::integral_constant<int, 1>{});
-        }
-        if (r < rend) step(r, std::integral_constant<int, 0>{});
+        uint32_t fa = 0, fd = 0;
+        if (fast) march<K, FLAGS, true>(A, fa, fd);
+        else march<K, FLAGS, false>(A, fa, fd);
 
         if (FLAGS) {
-            const bool a = __any_sync(0xffffffffu, acc_alive != 0);
-            const bool d = __any_sync(0xffffffffu, acc_diff != 0);
+            const bool a = __any_sync(0xffffffffu, fa != 0);
+            const bool d = __any_sync(0xffffffffu, fd != 0);
             if (lane == 0) {
                 if (a) atomicOr(&D.scratch->alive, 1u);
                 if (d) atomicOr(&D.scratch->diff, 1u);
