@@ -83,7 +83,7 @@ struct gol_engine {
     uint32_t *d_dflags = nullptr;  // [kMaxBatch + 1][2]
     uint32_t *h_dflags = nullptr;  // pinned
 
-    int cur = 0;
+    int cur = 0, prev_in = -1;
     uint32_t seq = 0, rec_seq = 0;
     bool prepared = false;
     int64_t launches = 0;
@@ -247,22 +247,20 @@ int launch_epoch(gol_engine *e, int k, int in, int out, bool flags, int rec_slot
 // written.  With want_flags the last epoch publishes a record (rec slot/seq returned).
 int run_epochs(gol_engine *e, int64_t n, int keep, bool want_flags, bool per_gen_flags, int kcap)
 {
-    int a = -1, b = -1;
-    for (int i = 0; i < GOL_NBUF && b < 0; ++i) {
-        if (i == keep || i == e->cur) continue;
-        if (a < 0) a = i; else b = i;
-    }
+    // Output buffers rotate over the buffers that are neither the epoch's input, nor the
+    // previous epoch's input (a neighbouring rank may still be reading it: flags are published
+    // as soon as the border items are done, not at the end of the launch), nor `keep`.
     int in = e->cur;
     int64_t left = n;
-    int which = 0;
     while (left > 0) {
         int k = 1;
         if (!per_gen_flags) {
             const int cap = (int)std::min<int64_t>(left, kcap);
             while (k * 2 <= cap) k *= 2;
         }
-        int out = which ? b : a;
-        if (out == in) out = which ? a : b;
+        int out = -1;
+        for (int i = 0; i < GOL_NBUF; ++i)
+            if (i != in && i != e->prev_in && i != keep) { out = i; break; }
         const bool last = left - k == 0;
         const bool f = per_gen_flags || (want_flags && last);
         uint32_t rs = 0;
@@ -279,8 +277,8 @@ int run_epochs(gol_engine *e, int64_t n, int keep, bool want_flags, bool per_gen
                                       rs, e->d_results + (n - left), e->d_error, e->stream));
             ++e->launches;
         }
+        e->prev_in = in;
         in = out;
-        which ^= 1;
         left -= k;
     }
     e->cur = in;

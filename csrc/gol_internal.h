@@ -74,6 +74,7 @@ struct GolScratch {            // per-domain device scratch (zero between launch
     unsigned int alive;        // OR of final-level cells
     unsigned int diff;         // OR of final-level (old ^ new)
     unsigned int error;        // sticky: flag-wait timeout etc.
+    unsigned int border_done;  // border work items finished in the current launch
 };
 
 struct GolDomainDev {

@@ -130,7 +130,9 @@ __device__ void push_borders(const GolDomainDev &D, int o, int strip, int y0, in
                     outw[j] = val;
                 }
                 uint32_t *d = nb.buf[o] + (int64_t)drow * nb.pitch32 + GOL_GHOST_WORDS32 + nb.nw32;
-                d[0] = outw[0]; d[1] = outw[1]; d[2] = outw[2]; d[3] = outw[3];
+                // slot is 8-byte aligned (nw32 is even): two 64-bit stores
+                *reinterpret_cast<uint2 *>(d) = make_uint2(outw[0], outw[1]);
+                *reinterpret_cast<uint2 *>(d + 2) = make_uint2(outw[2], outw[3]);
             }
         }
         if (last) {
@@ -151,7 +153,7 @@ __device__ void push_borders(const GolDomainDev &D, int o, int strip, int y0, in
                 else { if (y < H - G) continue; dir = 7; drow = G + y - H; }
                 const GolNeighbor &nb = D.nb[dir];
                 uint32_t *d = nb.buf[o] + (int64_t)drow * nb.pitch32;
-                d[0] = outw[0]; d[1] = outw[1]; d[2] = outw[2]; d[3] = outw[3];
+                *reinterpret_cast<uint4 *>(d) = make_uint4(outw[0], outw[1], outw[2], outw[3]);
             }
         }
     }
@@ -175,27 +177,77 @@ __device__ void wait_neighbors(const GolDomainDev &D, uint32_t want, int lane)
     __threadfence();  // acquire for the whole warp: drop stale L1 lines of the ghost zones
 }
 
-// CTA epilogue: count finished CTAs of this domain; the last one publishes records and flags.
+// Work items of a domain are (strip, chunk) pairs.  They are numbered so that every item that
+// touches a ghost zone or pushes to a neighbour comes first: the top and bottom chunks, then
+// the first/last strip of the middle chunks, then the interior.  Border pushes therefore leave
+// at the very start of a launch and the neighbours' flags are published long before the
+// interior is done - the halo exchange is hidden behind the interior items.
+struct ItemMap {
+    int S, chunks, top, first_bot, nborder;
+};
+__device__ __forceinline__ ItemMap item_map(const GolDomainDev &D, int chunk_rows)
+{
+    ItemMap m;
+    m.S = D.strips;
+    m.chunks = (D.H + chunk_rows - 1) / chunk_rows;
+    m.top = min(m.chunks, (G + chunk_rows - 1) / chunk_rows);           // chunks with y0 < G
+    m.first_bot = min(m.chunks, max(m.top, (D.H - G) / chunk_rows));    // first chunk with y1 > H - G
+    const int mid = m.first_bot - m.top;
+    m.nborder = (m.chunks - mid) * m.S + mid * min(m.S, 2);
+    return m;
+}
+// returns false for idle items (beyond this domain's item count)
+__device__ __forceinline__ bool decode_item(const ItemMap &m, int item, int &strip, int &chunk, bool &border)
+{
+    const int S = m.S, n1 = m.top * S, n2 = (m.chunks - m.first_bot) * S, mid = m.first_bot - m.top;
+    const int e = min(S, 2), n3 = mid * e;
+    border = true;
+    if (item < n1) { chunk = item / S; strip = item - chunk * S; return true; }
+    item -= n1;
+    if (item < n2) { const int c = item / S; chunk = m.first_bot + c; strip = item - c * S; return true; }
+    item -= n2;
+    if (item < n3) { const int c = item / e; chunk = m.top + c; strip = (item - c * e) ? S - 1 : 0; return true; }
+    item -= n3;
+    border = false;
+    if (S <= 2 || item >= mid * (S - 2)) return false;
+    const int c = item / (S - 2);
+    chunk = m.top + c;
+    strip = 1 + item - c * (S - 2);
+    return true;
+}
+
+// Called by every border warp after its pushes: the last one publishes the epoch flags.
+__device__ __forceinline__ void border_item_done(const GolDomainDev &D, const GolLaunch &lp, int nborder, int lane)
+{
+    __threadfence_system();  // my pushes are visible system-wide before the count / the flags
+    __syncwarp();
+    if (lane == 0) {
+        const unsigned prev = atomicAdd(&D.scratch->border_done, 1u);
+        if (prev == (unsigned)nborder - 1) {
+            D.scratch->border_done = 0;
+            __threadfence_system();
+            for (int d = 0; d < GOL_NDIR; ++d) st_release_sys(D.nb[d].flag, lp.seq);
+        }
+    }
+}
+
+// CTA epilogue for launches that publish a flag record: the last CTA of the domain does it.
 __device__ void finish_domain(const GolDomainDev &D, const GolLaunch &lp)
 {
     __syncthreads();
     if (threadIdx.x != 0) return;
-    __threadfence_system();
+    __threadfence();
     const unsigned prev = atomicAdd(&D.scratch->done, 1u);
     if (prev != (unsigned)lp.ctas_per_domain - 1) return;
-    __threadfence_system();
-    if (lp.rec_slot >= 0) {
-        const unsigned a = atomicExch(&D.scratch->alive, 0u);
-        const unsigned d = atomicExch(&D.scratch->diff, 0u);
-        const unsigned long long rec =
-            ((unsigned long long)lp.rec_seq << 32) | (a ? 1ull : 0ull) | (d ? 2ull : 0ull);
-        for (int p = 0; p < D.proc_count; ++p) {
-            unsigned long long *t = D.rec_tables[p] + (int64_t)lp.rec_slot * D.num_domains + D.global_id;
-            asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(t), "l"(rec) : "memory");
-        }
+    __threadfence();
+    const unsigned a = atomicExch(&D.scratch->alive, 0u);
+    const unsigned d = atomicExch(&D.scratch->diff, 0u);
+    const unsigned long long rec =
+        ((unsigned long long)lp.rec_seq << 32) | (a ? 1ull : 0ull) | (d ? 2ull : 0ull);
+    for (int p = 0; p < D.proc_count; ++p) {
+        unsigned long long *t = D.rec_tables[p] + (int64_t)lp.rec_slot * D.num_domains + D.global_id;
+        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(t), "l"(rec) : "memory");
     }
-    if (lp.signal)
-        for (int d = 0; d < GOL_NDIR; ++d) st_release_sys(D.nb[d].flag, lp.seq);
     D.scratch->done = 0;
     __threadfence();
 }
@@ -352,23 +404,22 @@ __global__ void __launch_bounds__(kWarps * 32) life_strip_kernel(const GolDomain
     const GolDomainDev &D = doms[dom_id];
     const int lane = threadIdx.x & 31;
     const int item = cta * kWarps + (threadIdx.x >> 5);
-    const int S = D.strips;
-    const int strip = item % S, chunk = item / S;
-    const int H = D.H;
+    const ItemMap im = item_map(D, lp.chunk_rows);
+    const int S = im.S, H = D.H;
+    int strip = 0, chunk = 0;
+    bool border = false;
+    const bool active = decode_item(im, item, strip, chunk, border);
     const int y0 = chunk * lp.chunk_rows;
     const int y1 = min(H, y0 + lp.chunk_rows);
-    const bool need_done = lp.signal || lp.rec_slot >= 0;
 
-    if (chunk < lp.chunks && y0 < H) {
+    if (active) {
         MarchArgs A;
         A.nw = D.nw32; A.nwf = D.nwf32; A.rem = D.rem; A.pitch = D.pitch32;
         A.in = reinterpret_cast<const uint32_t *>(__cvta_generic_to_global(D.buf[lp.in_idx]));
         A.out = reinterpret_cast<uint32_t *>(__cvta_generic_to_global(D.buf[lp.out_idx]));
         A.vi = strip_origin(strip, S, A.nw) - kWL + lane * kWL;
         A.y0 = y0; A.y1 = y1;
-        const bool reads_ghosts = strip == 0 || strip == S - 1 || y0 - K < 0 || y1 + K > H;
-        const bool border = strip == 0 || strip == S - 1 || y0 < G || y1 > H - G;
-        if (lp.wait_seq && reads_ghosts) wait_neighbors(D, lp.wait_seq, lane);
+        if (lp.wait_seq && border) wait_neighbors(D, lp.wait_seq, lane);
 
         // per-lane constants
         const bool owned_lane = lane >= 1 && lane <= kValidLanes;
@@ -401,10 +452,12 @@ __global__ void __launch_bounds__(kWarps * 32) life_strip_kernel(const GolDomain
             }
         }
         __syncwarp();
-        if (border) push_borders(D, lp.out_idx, strip, y0, y1, lane);
-        if (need_done) __threadfence_system();
+        if (border) {
+            push_borders(D, lp.out_idx, strip, y0, y1, lane);
+            if (lp.signal) border_item_done(D, lp, im.nborder, lane);
+        }
     }
-    if (need_done) finish_domain(D, lp);
+    if (lp.rec_slot >= 0) finish_domain(D, lp);
 }
 
 // ------------------------------------------------------------- halo kernel
@@ -416,16 +469,14 @@ __global__ void __launch_bounds__(kWarps * 32) halo_push_kernel(const GolDomainD
     const GolDomainDev &D = doms[dom_id];
     const int lane = threadIdx.x & 31;
     const int item = cta * kWarps + (threadIdx.x >> 5);
-    const int S = D.strips;
-    const int strip = item % S, chunk = item / S;
+    const ItemMap im = item_map(D, lp.chunk_rows);
+    int strip = 0, chunk = 0;
+    bool border = false;
+    if (!decode_item(im, item, strip, chunk, border) || !border) return;
     const int y0 = chunk * lp.chunk_rows;
     const int y1 = min(D.H, y0 + lp.chunk_rows);
-    if (chunk < lp.chunks && y0 < D.H) {
-        const bool border = strip == 0 || strip == S - 1 || y0 < G || y1 > D.H - G;
-        if (border) push_borders(D, lp.out_idx, strip, y0, y1, lane);
-        __threadfence_system();
-    }
-    finish_domain(D, lp);
+    push_borders(D, lp.out_idx, strip, y0, y1, lane);
+    if (lp.signal) border_item_done(D, lp, im.nborder, lane);
 }
 
 // ------------------------------------------------------------- alive scan
@@ -438,11 +489,13 @@ __global__ void __launch_bounds__(kWarps * 32) scan_alive_kernel(const GolDomain
     const GolDomainDev &D = doms[dom_id];
     const int lane = threadIdx.x & 31;
     const int item = cta * kWarps + (threadIdx.x >> 5);
-    const int S = D.strips;
-    const int strip = item % S, chunk = item / S;
-    const int y0 = chunk * lp.chunk_rows;
-    const int y1 = min(D.H, y0 + lp.chunk_rows);
-    if (chunk < lp.chunks && y0 < D.H) {
+    const ItemMap im = item_map(D, lp.chunk_rows);
+    const int S = im.S;
+    int strip = 0, chunk = 0;
+    bool border = false;
+    if (decode_item(im, item, strip, chunk, border)) {
+        const int y0 = chunk * lp.chunk_rows;
+        const int y1 = min(D.H, y0 + lp.chunk_rows);
         const int lo = strip_origin(strip, S, D.nw32), hi = min(D.nw32, lo + kVW);
         const uint32_t *src = D.buf[lp.in_idx];
         uint32_t acc = 0;
