@@ -14,7 +14,7 @@ NVFLAGS   := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC,-Wall,-Wno-unused
 CXXFLAGS  := -O3 -std=c++17 -fPIC -Wall -pthread
 BUILD     := build
 LIB       := libgolb200.so
-CU_SRCS   := csrc/life_kernels.cu csrc/dense_kernels.cu csrc/engine.cu
+CU_SRCS   := csrc/life_kernels.cu csrc/dense_kernels.cu csrc/engine.cu csrc/static_scratch.cu
 CPP_SRCS  := csrc/host_util.cpp
 OBJS      := $(CU_SRCS:csrc/%.cu=$(BUILD)/%.o) $(CPP_SRCS:csrc/%.cpp=$(BUILD)/%.o)
 HDRS      := include/gol_b200.h csrc/gol_internal.h csrc/life_rule.h

@@ -226,6 +226,25 @@ int64_t gol_engine_launch_count(const gol_engine *e);
 /* Local population / flags of the current buffer. */
 int gol_engine_population(gol_engine *e, uint64_t *count);
 
+/* Same result as gol_engine_population, for callers that may not allocate device memory: a
+ * process whose GPU memory is owned wholesale by another allocator (a framework pool), where a
+ * raw cudaMalloc fails or fights the pool, and latency-bound loops, where the device-wide
+ * synchronisation inside cudaMalloc / cudaFree is not affordable.  (No counterpart in the
+ * reference.)  It calls no cudaMalloc, cudaFree or allocating library routine: the dense
+ * staging copy and the counter live in a static device array of GOL_STATIC_SCRATCH_BYTES + 256
+ * bytes inside the library image, present on every GPU that loads the library until exit.
+ *  - limit: each local domain must fit the staging area, ceil(w/64) * 8 * h <= 4 MiB
+ *    (32 Mi cells, e.g. 4096 x 8192); larger domains are rejected with an error and nothing
+ *    is launched.
+ *  - the first call on a device looks the array's address up (cudaGetSymbolAddress) and keeps
+ *    it; make that first call before any stream capture begins.
+ *  - all calls share the one array and it keeps the last call's contents; the counter is
+ *    cleared at the start of every call.  Calls that overlap on the GPU (from several threads
+ *    or engines) race on it: serialise them.
+ *  - runs on the calling thread's per-thread default stream after synchronising the engine. */
+#define GOL_STATIC_SCRATCH_BYTES (4u << 20)
+int gol_engine_population_static(gol_engine *e, uint64_t *count);
+
 /* Zero-copy access to a local domain's current padded buffer (for the PyTorch
  * tensor view): device pointer to padded word (row 0, word 0) + its layout. */
 int gol_engine_domain_buffer(gol_engine *e, int local_index, void **d_ptr, gol_layout *layout);
