@@ -69,3 +69,40 @@ def run_program(exe: str, width: int, height: int, input_path: str, workdir: str
     with open(os.path.join(workdir, output_name), "rb") as f:
         out = f.read()
     return (int(gens.group(1)) if gens else None, float(ms.group(1)) if ms else None, out, p.stdout)
+
+
+MPI_VARIANTS = {"mpi": "mpi_output.out", "collective": "collective_output.out", "async": "async_output.out",
+                "openmp": "openmp_output.out"}
+
+
+def build_mpi() -> dict | None:
+    """The four MPI programs, unmodified, through the reference's own Makefile targets with the
+    single-node shim's mpicc (baseline/mpishim).  Returns {variant: exe, "mpiexec": launcher}."""
+    if stage_sources() is None:
+        return None
+    base = os.path.join(REPO_ROOT, "baseline")
+    exes = {v: os.path.join(REF_DIR, f"game_{v}") for v in MPI_VARIANTS}
+    launcher = os.path.join(base, "mpishim", "mpiexec")
+    if not all(os.path.exists(p) for p in list(exes.values()) + [launcher]):
+        subprocess.run(["make", "-C", base, "shim", "ref_mpi"], check=True, stdout=subprocess.DEVNULL,
+                       stderr=subprocess.DEVNULL)
+    exes["mpiexec"] = launcher
+    return exes
+
+
+def run_mpi(exes: dict, variant: str, ranks: int, width: int, input_path: str, workdir: str,
+            timeout: float | None = None):
+    """`mpiexec -n ranks ./a.out W W input` for an MPI variant under the shim; same return as run_program
+    plus the 'Reading file' / 'Writing file' times in a dict."""
+    p = subprocess.run([exes["mpiexec"], "-n", str(ranks), exes[variant], str(width), str(width),
+                        os.path.abspath(input_path)], cwd=workdir, capture_output=True, text=True, timeout=timeout,
+                       check=True)
+    gens = re.search(r"Generations:\s+(\d+)", p.stdout)
+    ms = re.search(r"Execution time:\s+([0-9.]+)", p.stdout)
+    rd = re.search(r"Reading file:\s+([0-9.]+)", p.stdout)
+    wr = re.search(r"Writing file:\s+([0-9.]+)", p.stdout)
+    with open(os.path.join(workdir, MPI_VARIANTS[variant]), "rb") as f:
+        out = f.read()
+    return (int(gens.group(1)) if gens else None, float(ms.group(1)) if ms else None, out,
+            {"read_ms": float(rd.group(1)) if rd else None, "write_ms": float(wr.group(1)) if wr else None,
+             "stdout": p.stdout})
