@@ -44,6 +44,7 @@ struct ArenaLayout {
     std::vector<int64_t> buf_off;     // [local domain][GOL_NBUF] byte offsets
     std::vector<int64_t> flags_off;   // [local domain]
     std::vector<int64_t> scratch_off; // [local domain]
+    std::vector<int64_t> items_off;   // [local domain] per-item epoch flags (persistent kernel)
     int64_t rec_off = 0;
     int64_t total = 0;
 };
@@ -77,6 +78,9 @@ struct gol_engine {
     unsigned int *d_error = nullptr;
     int max_strips = 1;
     int64_t max_h = 1;
+    int64_t items_cap = 0;          // per-domain capacity of the item flag array
+    bool use_persistent = false;    // GOL_PERSISTENT=1: one dataflow launch per batch instead of one per epoch
+    int persist_ctas[9] = {0};      // max co-resident CTAs of the persistent kernel per k (0 = not queried)
 
     // dense path (tiny grids, single domain)
     uint64_t *dense[3] = {nullptr, nullptr, nullptr};
@@ -122,6 +126,7 @@ int build_arena_layout(const gol_engine *e, int p, ArenaLayout *A)
     A->buf_off.assign((size_t)e->per_proc * GOL_NBUF, 0);
     A->flags_off.assign((size_t)e->per_proc, 0);
     A->scratch_off.assign((size_t)e->per_proc, 0);
+    A->items_off.assign((size_t)e->per_proc, 0);
     int64_t off = 0;
     for (int i = 0; i < e->per_proc; ++i) {
         const int gid = p * e->per_proc + i;
@@ -139,6 +144,8 @@ int build_arena_layout(const gol_engine *e, int p, ArenaLayout *A)
         off += 256;
         A->scratch_off[(size_t)i] = off;
         off += 256;
+        A->items_off[(size_t)i] = off;
+        off = align_up(off + (int64_t)e->items_cap * 4, 256);
     }
     A->rec_off = off;
     off = align_up(off + (int64_t)GOL_REC_SLOTS * e->ndom * 8, 256);
@@ -174,11 +181,13 @@ int upload_domains(gol_engine *e)
         D.global_id = ld.gid;
         D.epoch_flags = reinterpret_cast<uint32_t *>(e->arena + A.flags_off[(size_t)i]);
         D.scratch = reinterpret_cast<GolScratch *>(e->arena + A.scratch_off[(size_t)i]);
+        D.item_flags = reinterpret_cast<uint32_t *>(e->arena + A.items_off[(size_t)i]);
         D.rec_tables = e->d_rec_tables;
         D.proc_count = e->P;
         D.num_domains = e->ndom;
         for (int d = 0; d < GOL_NDIR; ++d) {
             const int ngid = neighbor_gid(e, ld.gid, d);
+            if (ngid == ld.gid) D.self_mask |= 1u << d;
             const int q = owner_of(e, ngid), li = ngid - q * e->per_proc;
             char *base = e->peer_arena[(size_t)q];
             GolNeighbor &N = D.nb[d];
@@ -204,11 +213,15 @@ int upload_domains(gol_engine *e)
 
 // Launch geometry for temporal depth k: chunk height trades apron redundancy (2k rows per
 // chunk) against the number of independent warps.
-void geometry(const gol_engine *e, int k, GolLaunch *lp)
+void geometry(const gol_engine *e, int k, GolLaunch *lp, int resident_warps_per_sm = 0)
 {
-    static const int warps_per_sm = getenv("GOL_WARPS_PER_SM") ? atoi(getenv("GOL_WARPS_PER_SM")) : 16;
+    static const int env_warps = getenv("GOL_WARPS_PER_SM") ? atoi(getenv("GOL_WARPS_PER_SM")) : 0;
+    const int warps_per_sm = env_warps ? env_warps : (resident_warps_per_sm ? resident_warps_per_sm : 16);
     const int64_t target_items = (int64_t)e->num_sms * warps_per_sm / std::max(1, e->per_proc);
-    int64_t chunks = std::max<int64_t>(1, (target_items + e->max_strips - 1) / e->max_strips);
+    // classic launches round up (a few CTAs more than slots is harmless); the persistent kernel
+    // must not exceed its resident warps, or some warps would carry two items per epoch
+    int64_t chunks = resident_warps_per_sm ? std::max<int64_t>(1, target_items / e->max_strips)
+                                           : std::max<int64_t>(1, (target_items + e->max_strips - 1) / e->max_strips);
     int64_t rows = gol_div_up(e->max_h, chunks);
     const int64_t min_rows = std::min<int64_t>(e->max_h, std::max<int64_t>(8, 6 * k));
     if (rows < min_rows) rows = min_rows;
@@ -252,6 +265,46 @@ int run_epochs(gol_engine *e, int64_t n, int keep, bool want_flags, bool per_gen
     // as soon as the border items are done, not at the end of the launch), nor `keep`.
     int in = e->cur;
     int64_t left = n;
+
+    // Leading run of full-depth epochs: one persistent (dataflow) launch instead of one launch
+    // per epoch.  The flagged last epoch of a batch and remainder epochs stay classic launches.
+    if (!per_gen_flags && e->use_persistent) {
+        int kp = 1;
+        while (kp * 2 <= std::min<int64_t>(left, kcap)) kp *= 2;
+        int64_t count = left / kp;
+        if (want_flags && count * kp == left) --count;
+        int rot[3], nrot = 0;
+        for (int i = 0; i < GOL_NBUF; ++i)
+            if (i != in && i != keep && i != e->prev_in && nrot < 3) rot[nrot++] = i;
+        if (e->prev_in >= 0 && e->prev_in != in && e->prev_in != keep && nrot < 3) rot[nrot++] = e->prev_in;  // written last
+        if (count >= 2 && kp <= 8 && nrot == 3) {
+            if (!e->persist_ctas[kp]) GOL_TRY(gol_persistent_max_ctas(kp, e->cfg.device, &e->persist_ctas[kp]));
+            GolLaunch g{};
+            geometry(e, kp, &g);
+            GolPersist pp{};
+            pp.epochs = (int32_t)std::min<int64_t>(count, 1 << 20);
+            pp.base_seq = e->seq;
+            pp.first_in = in;
+            pp.rot[0] = rot[0]; pp.rot[1] = rot[1]; pp.rot[2] = rot[2];
+            pp.chunk_rows = g.chunk_rows;
+            pp.items_per_domain = g.chunks * e->max_strips;
+            pp.ndoms = e->per_proc;
+            pp.wait_seq0 = multi(e) ? e->seq : 0;
+            const int64_t items = (int64_t)pp.ndoms * pp.items_per_domain;
+            if (pp.items_per_domain <= e->items_cap && e->persist_ctas[kp] > 0) {
+                const int ctas = (int)std::min<int64_t>(e->persist_ctas[kp], gol_div_up(items, 4));
+                pp.total_warps = ctas * 4;
+                pp.work_counter = e->d_error + 1;
+                GOL_CUDA(cudaMemsetAsync(pp.work_counter, 0, sizeof(unsigned int), e->stream));
+                GOL_TRY(gol_launch_persistent(e->d_doms, pp, kp, ctas, e->stream));
+                ++e->launches;
+                e->seq += (uint32_t)pp.epochs;
+                e->prev_in = pp.epochs >= 2 ? rot[(pp.epochs - 2) % 3] : in;
+                in = rot[(pp.epochs - 1) % 3];
+                left -= (int64_t)pp.epochs * kp;
+            }
+        }
+    }
     while (left > 0) {
         int k = 1;
         if (!per_gen_flags) {
@@ -296,6 +349,19 @@ int gather_last(gol_engine *e, int result_index)
     return 0;
 }
 
+// Sticky per-domain error words set by device-side waits that timed out.
+int check_device_errors(gol_engine *e)
+{
+    for (int i = 0; i < e->per_proc; ++i) {
+        GolScratch sc;
+        GOL_CUDA(cudaMemcpy(&sc, e->arena + e->arena_layout.scratch_off[(size_t)i], sizeof sc, cudaMemcpyDeviceToHost));
+        if (sc.error)
+            GOL_FAIL("device-side wait timed out in domain %d (code %u): a neighbouring work item or rank stopped "
+                     "making progress", e->local[(size_t)i].gid, sc.error);
+    }
+    return 0;
+}
+
 int fetch_results(gol_engine *e, int count)
 {
     GOL_CUDA(cudaMemcpyAsync(e->h_results, e->d_results, sizeof(unsigned long long) * (size_t)count,
@@ -306,7 +372,7 @@ int fetch_results(gol_engine *e, int count)
     GOL_CUDA(cudaStreamSynchronize(e->stream));
     err = (unsigned int)e->h_results[kMaxBatch + 1];
     if (err) GOL_FAIL("device-side wait timed out (code %u): a neighbouring rank stopped making progress", err);
-    return 0;
+    return check_device_errors(e);
 }
 
 // Literal evaluation of the serial loop (S:177-196) on per-generation flags.
@@ -569,6 +635,8 @@ static int engine_create_impl(gol_engine *e)
         e->max_strips = std::max(e->max_strips, s);
         e->max_h = std::max(e->max_h, h);
     }
+    e->items_cap = (int64_t)e->max_strips * gol_div_up(e->max_h, 8) + 64;
+    if (const char *v = getenv("GOL_PERSISTENT")) e->use_persistent = atoi(v) != 0;
     GOL_TRY(build_arena_layout(e, e->rank, &e->arena_layout));
     GOL_CUDA(cudaMalloc(&e->arena, (size_t)e->arena_layout.total));
     GOL_CUDA(cudaMemset(e->arena, 0, (size_t)e->arena_layout.total));
@@ -579,8 +647,8 @@ static int engine_create_impl(gol_engine *e)
     GOL_CUDA(cudaMalloc(&e->d_results, sizeof(unsigned long long) * (kMaxBatch + 2)));
     GOL_CUDA(cudaMemset(e->d_results, 0, sizeof(unsigned long long) * (kMaxBatch + 2)));
     GOL_CUDA(cudaMallocHost(&e->h_results, sizeof(unsigned long long) * (kMaxBatch + 2)));
-    GOL_CUDA(cudaMalloc(&e->d_error, sizeof(unsigned int)));
-    GOL_CUDA(cudaMemset(e->d_error, 0, sizeof(unsigned int)));
+    GOL_CUDA(cudaMalloc(&e->d_error, 2 * sizeof(unsigned int)));   // [0] error word, [1] persistent work counter
+    GOL_CUDA(cudaMemset(e->d_error, 0, 2 * sizeof(unsigned int)));
     if (e->P == 1) {
         GOL_TRY(upload_domains(e));
         e->imported = true;
@@ -1040,6 +1108,7 @@ int gol_engine_step(gol_engine *e, int64_t n)
         unsigned int err = 0;
         GOL_CUDA(cudaMemcpy(&err, e->d_error, 4, cudaMemcpyDeviceToHost));
         if (err) GOL_FAIL("device-side wait timed out (code %u)", err);
+        GOL_TRY(check_device_errors(e));
     }
     return 0;
 }

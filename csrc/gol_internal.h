@@ -84,11 +84,13 @@ struct GolDomainDev {
     int32_t global_id;
     GolNeighbor nb[GOL_NDIR];
     uint32_t *epoch_flags;     // [8] written by the neighbours (slot d = neighbour in direction d)
+    uint32_t *item_flags;      // [items] sequence of the last epoch each work item completed (persistent kernel)
     GolScratch *scratch;
     // flag records: rec_tables[p] = table of process p (local or peer-mapped),
     // entry [slot * num_domains + global_id]
     unsigned long long **rec_tables;   // device array [proc_count]
     int32_t proc_count, num_domains;
+    uint32_t self_mask;        // bit d set: the neighbour in direction d is this domain itself (torus wrap)
 };
 
 struct GolLaunch {
@@ -102,6 +104,22 @@ struct GolLaunch {
     uint32_t rec_seq;
 };
 
+// Persistent (dataflow) launch: `epochs` epochs of K generations in ONE kernel; work items wait
+// for their 3x3 neighbourhood of the previous epoch through per-item flags instead of a
+// kernel boundary.
+struct GolPersist {
+    int32_t epochs;
+    uint32_t base_seq;         // epoch e carries sequence base_seq + 1 + e
+    int32_t first_in;          // buffer read by epoch 0
+    int32_t rot[3];            // epoch e writes rot[e % 3] (and reads rot[(e-1) % 3] for e > 0)
+    int32_t chunk_rows;
+    int32_t items_per_domain;  // uniform (padded) item count per domain
+    int32_t ndoms;
+    int32_t total_warps;
+    uint32_t wait_seq0;        // ghost-flag sequence epoch 0's border items wait for (0 = none)
+    unsigned int *work_counter; // device word, zero at launch: next (epoch, item) to hand out
+};
+
 // ------------------------------------------------------------ kernel entry
 // (implemented in life_kernels.cu)
 struct CUstream_st;
@@ -110,6 +128,8 @@ int gol_launch_strip(const GolDomainDev *d_doms, int ndoms, const GolLaunch &lp,
 int gol_launch_halo(const GolDomainDev *d_doms, int ndoms, const GolLaunch &lp, int max_rows,
                     CUstream_st *stream);
 int gol_strip_geometry(int nw32, int *strips);
+int gol_persistent_max_ctas(int k, int device, int *ctas);
+int gol_launch_persistent(const GolDomainDev *d_doms, const GolPersist &pp, int k, int ctas, CUstream_st *stream);
 int gol_launch_scan_alive(const GolDomainDev *d_doms, int ndoms, const GolLaunch &lp, CUstream_st *stream);
 int gol_write_all(int fd, const char *buf, size_t len, int64_t offset, const char *path);
 int gol_launch_gather(unsigned long long *rec_table, int slot, int num_domains, uint32_t seq,

@@ -63,6 +63,36 @@ __device__ __forceinline__ uint32_t life_rule(uint32_t a0, uint32_t a1, uint32_t
     return lop3<0xEA>(x0, g, u);                 // (x0 & g) | u
 }
 
+// Experiment kept for the record (off): funnel shifts by one bit on the FMA pipe instead of the
+// ALU pipe that the LOP3 adder saturates: (cur << 1) | (prev >> 31) = cur * 2 + hi32(prev * 2),
+// (cur >> 1) | (next << 31) = hi32(cur * 2^31) + lo32(next * 2^31).  Measured on B200: slower
+// (K=8: 11.03 vs 10.27 us/generation at 16384^2) - IMAD.HI costs more than the SHF it replaces.
+#ifndef GOL_IMAD_SHIFTS
+#define GOL_IMAD_SHIFTS 0
+#endif
+__device__ __forceinline__ uint32_t shl1_in(uint32_t prev, uint32_t cur)
+{
+#if GOL_IMAD_SHIFTS
+    uint32_t t, d;
+    asm("mul.hi.u32 %0, %1, 2;" : "=r"(t) : "r"(prev));
+    asm("mad.lo.u32 %0, %1, 2, %2;" : "=r"(d) : "r"(cur), "r"(t));
+    return d;
+#else
+    return __funnelshift_l(prev, cur, 1);
+#endif
+}
+__device__ __forceinline__ uint32_t shr1_in(uint32_t cur, uint32_t next)
+{
+#if GOL_IMAD_SHIFTS
+    uint32_t t, d;
+    asm("mul.lo.u32 %0, %1, 0x80000000;" : "=r"(t) : "r"(next));
+    asm("mad.hi.u32 %0, %1, 0x80000000, %2;" : "=r"(d) : "r"(cur), "r"(t));
+    return d;
+#else
+    return __funnelshift_r(cur, next, 1);
+#endif
+}
+
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p)
 {
     uint32_t v;
@@ -160,13 +190,13 @@ __device__ void push_borders(const GolDomainDev &D, int o, int strip, int y0, in
 }
 
 // Spin until the 8 neighbours have published sequence >= want into my epoch flags.
-__device__ void wait_neighbors(const GolDomainDev &D, uint32_t want, int lane)
+__device__ void wait_neighbors(const GolDomainDev &D, uint32_t want, int lane, uint32_t skip_mask = 0)
 {
-    if (lane < GOL_NDIR) {
+    if (lane < GOL_NDIR && !((skip_mask >> lane) & 1u)) {
         const uint32_t *f = D.epoch_flags + lane;
         long long t0 = clock64();
         while ((int32_t)(ld_acquire_sys(f) - want) < 0) {
-            if (clock64() - t0 > (1ll << 33)) {  // ~4 s: neighbour is gone
+            if (clock64() - t0 > (1ll << 32) || *(volatile unsigned int *)&D.scratch->error) {  // ~2 s: neighbour is gone
                 atomicOr(&D.scratch->error, 1u);
                 break;
             }
@@ -347,8 +377,8 @@ __device__ __forceinline__ void march(const MarchArgs &A, uint32_t &flag_alive, 
             for (int j = 0; j < kWL; ++j) {
                 const uint32_t pw = j ? cur[j - 1] : left;
                 const uint32_t nx = j < kWL - 1 ? cur[j + 1] : right;
-                const uint32_t L = __funnelshift_l(pw, cur[j], 1);
-                const uint32_t R = __funnelshift_r(cur[j], nx, 1);
+                const uint32_t L = shl1_in(pw, cur[j]);
+                const uint32_t R = shr1_in(cur[j], nx);
                 const uint32_t s0 = xor3(L, cur[j], R);
                 const uint32_t s1 = maj3(L, cur[j], R);
                 // rows r-t-2 (slot PAR), r-t-1 (slot PAR^1, centre ctr[t]) and r-t (s0,s1)
@@ -395,6 +425,71 @@ __device__ __forceinline__ void march(const MarchArgs &A, uint32_t &flag_alive, 
     }
 }
 
+struct ItemCtx {
+    int in_idx, out_idx;
+    uint32_t seq, wait_seq;
+    int signal, chunk_rows;
+    uint32_t skip_mask;   // ghost flags not to wait for (directions covered by item-level waits)
+};
+
+// One work item: (optionally) wait for the neighbours' ghost pushes, stream the chunk through K
+// levels, accumulate flags, push the borders and count the item towards the epoch flag.
+template <int K, bool FLAGS>
+__device__ __forceinline__ void run_item(const GolDomainDev &D, const ItemCtx &c, const ItemMap &im, int strip,
+                                         int chunk, bool border, int lane)
+{
+    const int S = im.S, H = D.H;
+    const int y0 = chunk * c.chunk_rows;
+    const int y1 = min(H, y0 + c.chunk_rows);
+    MarchArgs A;
+    A.nw = D.nw32; A.nwf = D.nwf32; A.rem = D.rem; A.pitch = D.pitch32;
+    A.in = reinterpret_cast<const uint32_t *>(__cvta_generic_to_global(D.buf[c.in_idx]));
+    A.out = reinterpret_cast<uint32_t *>(__cvta_generic_to_global(D.buf[c.out_idx]));
+    A.vi = strip_origin(strip, S, A.nw) - kWL + lane * kWL;
+    A.y0 = y0; A.y1 = y1;
+    if (c.wait_seq && border) wait_neighbors(D, c.wait_seq, lane, c.skip_mask);
+
+    // per-lane constants
+    const bool owned_lane = lane >= 1 && lane <= kValidLanes;
+#pragma unroll
+    for (int j = 0; j < kWL; ++j) {
+        const int i = A.vi + j;
+        uint32_t kmask = (owned_lane && i >= 0 && i < A.nw) ? 0xffffffffu : 0u;
+        if (A.rem) {
+            if (i == A.nwf) kmask &= A.rem >= 32 ? 0xffffffffu : ((1u << A.rem) - 1u);
+            if (i == A.nwf + 1) kmask &= A.rem > 32 ? ((1u << (A.rem - 32)) - 1u) : 0u;
+        }
+        A.keep[j] = kmask;
+    }
+    // load mode: 1 = plain vector load, 2 = composed tail (partial word + shifted ghost), 0 = none
+    if (A.rem == 0) A.mode = (A.vi >= -GOL_GHOST_WORDS32 && A.vi + kWL <= A.nw + GOL_GHOST_WORDS32) ? 1 : 0;
+    else A.mode = (A.vi >= -GOL_GHOST_WORDS32 && A.vi + kWL <= A.nwf) ? 1 : (A.vi < A.nwf + 4 && A.vi + kWL > A.nwf ? 2 : 0);
+    const bool all_or_none = (A.keep[0] & A.keep[1]) == 0xffffffffu || (A.keep[0] | A.keep[1]) == 0u;
+    const bool fast = __all_sync(0xffffffffu, A.mode == 1 && all_or_none);
+
+    uint32_t fa = 0, fd = 0;
+    if (fast) march<K, FLAGS, true>(A, fa, fd);
+    else march<K, FLAGS, false>(A, fa, fd);
+
+    if (FLAGS) {
+        const bool a = __any_sync(0xffffffffu, fa != 0);
+        const bool d = __any_sync(0xffffffffu, fd != 0);
+        if (lane == 0) {
+            if (a) atomicOr(&D.scratch->alive, 1u);
+            if (d) atomicOr(&D.scratch->diff, 1u);
+        }
+    }
+    __syncwarp();
+    if (border) {
+        push_borders(D, c.out_idx, strip, y0, y1, lane);
+        if (c.signal) {
+            GolLaunch lp;
+            lp.seq = c.seq;
+            border_item_done(D, lp, im.nborder, lane);
+        }
+    }
+}
+
 template <int K, bool FLAGS>
 __global__ void __launch_bounds__(kWarps * 32) life_strip_kernel(const GolDomainDev *__restrict__ doms,
                                                                  const GolLaunch lp)
@@ -405,59 +500,122 @@ __global__ void __launch_bounds__(kWarps * 32) life_strip_kernel(const GolDomain
     const int lane = threadIdx.x & 31;
     const int item = cta * kWarps + (threadIdx.x >> 5);
     const ItemMap im = item_map(D, lp.chunk_rows);
-    const int S = im.S, H = D.H;
     int strip = 0, chunk = 0;
     bool border = false;
-    const bool active = decode_item(im, item, strip, chunk, border);
-    const int y0 = chunk * lp.chunk_rows;
-    const int y1 = min(H, y0 + lp.chunk_rows);
-
-    if (active) {
-        MarchArgs A;
-        A.nw = D.nw32; A.nwf = D.nwf32; A.rem = D.rem; A.pitch = D.pitch32;
-        A.in = reinterpret_cast<const uint32_t *>(__cvta_generic_to_global(D.buf[lp.in_idx]));
-        A.out = reinterpret_cast<uint32_t *>(__cvta_generic_to_global(D.buf[lp.out_idx]));
-        A.vi = strip_origin(strip, S, A.nw) - kWL + lane * kWL;
-        A.y0 = y0; A.y1 = y1;
-        if (lp.wait_seq && border) wait_neighbors(D, lp.wait_seq, lane);
-
-        // per-lane constants
-        const bool owned_lane = lane >= 1 && lane <= kValidLanes;
-#pragma unroll
-        for (int j = 0; j < kWL; ++j) {
-            const int i = A.vi + j;
-            uint32_t kmask = (owned_lane && i >= 0 && i < A.nw) ? 0xffffffffu : 0u;
-            if (A.rem) {
-                if (i == A.nwf) kmask &= A.rem >= 32 ? 0xffffffffu : ((1u << A.rem) - 1u);
-                if (i == A.nwf + 1) kmask &= A.rem > 32 ? ((1u << (A.rem - 32)) - 1u) : 0u;
-            }
-            A.keep[j] = kmask;
-        }
-        // load mode: 1 = plain vector load, 2 = composed tail (partial word + shifted ghost), 0 = none
-        if (A.rem == 0) A.mode = (A.vi >= -GOL_GHOST_WORDS32 && A.vi + kWL <= A.nw + GOL_GHOST_WORDS32) ? 1 : 0;
-        else A.mode = (A.vi >= -GOL_GHOST_WORDS32 && A.vi + kWL <= A.nwf) ? 1 : (A.vi < A.nwf + 4 && A.vi + kWL > A.nwf ? 2 : 0);
-        const bool all_or_none = (A.keep[0] & A.keep[1]) == 0xffffffffu || (A.keep[0] | A.keep[1]) == 0u;
-        const bool fast = __all_sync(0xffffffffu, A.mode == 1 && all_or_none);
-
-        uint32_t fa = 0, fd = 0;
-        if (fast) march<K, FLAGS, true>(A, fa, fd);
-        else march<K, FLAGS, false>(A, fa, fd);
-
-        if (FLAGS) {
-            const bool a = __any_sync(0xffffffffu, fa != 0);
-            const bool d = __any_sync(0xffffffffu, fd != 0);
-            if (lane == 0) {
-                if (a) atomicOr(&D.scratch->alive, 1u);
-                if (d) atomicOr(&D.scratch->diff, 1u);
-            }
-        }
-        __syncwarp();
-        if (border) {
-            push_borders(D, lp.out_idx, strip, y0, y1, lane);
-            if (lp.signal) border_item_done(D, lp, im.nborder, lane);
-        }
+    if (decode_item(im, item, strip, chunk, border)) {
+        ItemCtx c;
+        c.in_idx = lp.in_idx; c.out_idx = lp.out_idx; c.seq = lp.seq; c.wait_seq = lp.wait_seq;
+        c.signal = lp.signal; c.chunk_rows = lp.chunk_rows; c.skip_mask = 0;
+        run_item<K, FLAGS>(D, c, im, strip, chunk, border, lane);
     }
     if (lp.rec_slot >= 0) finish_domain(D, lp);
+}
+
+// ------------------------------------------------------- persistent kernel
+__device__ __forceinline__ int encode_item(const ItemMap &m, int strip, int chunk)
+{
+    const int S = m.S, n1 = m.top * S, n2 = (m.chunks - m.first_bot) * S, mid = m.first_bot - m.top;
+    const int e = min(S, 2), n3 = mid * e;
+    if (chunk < m.top) return chunk * S + strip;
+    if (chunk >= m.first_bot) return n1 + (chunk - m.first_bot) * S + strip;
+    const int c = chunk - m.top;
+    if (strip == 0) return n1 + n2 + c * e;
+    if (strip == S - 1) return n1 + n2 + c * e + (e - 1);
+    return n1 + n2 + n3 + c * (S - 2) + (strip - 1);
+}
+
+__device__ __forceinline__ uint32_t ld_acquire_gpu(const uint32_t *p)
+{
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// Wait until every item of this domain whose previous-epoch output this item reads has
+// completed `want`: strips s-1..s+1 x the chunks covering rows [y0-K, y1+K).  Directions in
+// which the domain is its own neighbour wrap around (single-domain torus); the others are
+// covered by the ghost-zone flags of the neighbouring domains.
+template <int K>
+__device__ __forceinline__ void wait_items(const GolDomainDev &D, const ItemMap &im, int strip, int chunk,
+                                           int chunk_rows, uint32_t want, int lane)
+{
+    const bool wrap_y = (D.self_mask & 3u) == 3u, wrap_x = (D.self_mask & 12u) == 12u;
+    if (lane < 18) {
+        const int H = D.H, y0 = chunk * chunk_rows, y1 = min(H, y0 + chunk_rows);
+        const int ci = lane % 6;
+        int c = -1;
+        if (ci < 3) {  // chunks inside the domain that intersect [y0-K, y1+K)
+            const int ca = max(0, y0 - K) / chunk_rows, cb = min(H - 1, y1 + K - 1) / chunk_rows;
+            if (ca + ci <= cb) c = ca + ci;
+        } else if (ci < 5) {  // rows above row 0 are the torus' last rows: up to two trailing chunks
+            if (wrap_y && y0 - K < 0) {
+                const int cw = (H - (K - y0)) / chunk_rows + (ci - 3);
+                if (cw < im.chunks) c = cw;
+            }
+        } else {  // rows below the last row are the torus' first rows: chunk 0 (chunk_rows >= K)
+            if (wrap_y && y1 + K > H) c = 0;
+        }
+        int s = strip + lane / 6 - 1;
+        if (wrap_x) s = (s + im.S) % im.S;
+        else if (s < 0 || s >= im.S) c = -1;
+        if (c >= 0) {
+            const uint32_t *f = D.item_flags + encode_item(im, s, c);
+            long long t0 = clock64();
+            while ((int32_t)(ld_acquire_gpu(f) - want) < 0) {
+                if (clock64() - t0 > (1ll << 32) || *(volatile unsigned int *)&D.scratch->error) {
+                    atomicOr(&D.scratch->error, 4u);
+                    break;
+                }
+                __nanosleep(100);
+            }
+        }
+    }
+    __syncwarp();
+}
+
+// All epochs of a batch in one launch.  Warps draw (epoch, item) pairs from one atomic counter
+// in epoch-major order; an item starts as soon as its own dependencies are met, so there is no
+// grid-wide barrier, no launch gap and no per-epoch tail, and faster SMs simply take more items.
+// Deadlock-free: the handed-out items are always a prefix of the global order, all of them are
+// held by resident warps (cooperative launch), and an item only waits for smaller indices.
+template <int K>
+__global__ void __launch_bounds__(kWarps * 32, K >= 8 ? 3 : 1) life_persistent_kernel(const GolDomainDev *__restrict__ doms,
+                                                                      const GolPersist P)
+{
+    const int lane = threadIdx.x & 31;
+    const unsigned items_total = (unsigned)(P.ndoms * P.items_per_domain);
+    const unsigned total = items_total * (unsigned)P.epochs;
+    for (;;) {
+        // dynamic hand-out in global (epoch-major, border-first) order: fast SMs take more items
+        unsigned g = 0;
+        if (lane == 0) g = atomicAdd(P.work_counter, 1u);
+        g = __shfl_sync(0xffffffffu, g, 0);
+        if (g >= total) break;
+        const int e = (int)(g / items_total);
+        const int i = (int)(g - (unsigned)e * items_total);
+        const int dom = i / P.items_per_domain, item = i - dom * P.items_per_domain;
+        const GolDomainDev &D = doms[dom];
+        const ItemMap im = item_map(D, P.chunk_rows);
+        int strip = 0, chunk = 0;
+        bool border = false;
+        if (!decode_item(im, item, strip, chunk, border)) continue;
+        ItemCtx c;
+        c.in_idx = e == 0 ? P.first_in : P.rot[(e - 1) % 3];
+        c.out_idx = P.rot[e % 3];
+        c.seq = P.base_seq + 1 + (uint32_t)e;
+        c.wait_seq = e == 0 ? P.wait_seq0 : P.base_seq + (uint32_t)e;
+        c.signal = 1;
+        c.chunk_rows = P.chunk_rows;
+        // inside the launch, self-directions are tracked item by item; ghost flags are only
+        // awaited from directions where the neighbour is another domain
+        c.skip_mask = e == 0 ? 0u : D.self_mask;
+        if (e > 0) wait_items<K>(D, im, strip, chunk, P.chunk_rows, P.base_seq + (uint32_t)e, lane);
+        run_item<K, false>(D, c, im, strip, chunk, border, lane);
+        __threadfence();
+        __syncwarp();
+        if (lane == 0)
+            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(D.item_flags + item), "r"(c.seq) : "memory");
+    }
 }
 
 // ------------------------------------------------------------- halo kernel
@@ -599,6 +757,47 @@ int gol_launch_strip(const GolDomainDev *d_doms, int ndoms, const GolLaunch &lp,
     }
 #undef GOL_CASE
     if (err != cudaSuccess) GOL_FAIL("life_strip_kernel<k=%d> launch failed: %s", k, cudaGetErrorString(err));
+    return 0;
+}
+
+template <int K>
+static cudaError_t persistent_occupancy(int *ctas_per_sm)
+{
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, life_persistent_kernel<K>, kWarps * 32, 0);
+}
+
+int gol_persistent_max_ctas(int k, int device, int *ctas)
+{
+    int per_sm = 0, sms = 0;
+    cudaError_t err = cudaSuccess;
+    switch (k) {
+    case 1: err = persistent_occupancy<1>(&per_sm); break;
+    case 2: err = persistent_occupancy<2>(&per_sm); break;
+    case 4: err = persistent_occupancy<4>(&per_sm); break;
+    case 8: err = persistent_occupancy<8>(&per_sm); break;
+    default: GOL_FAIL("persistent kernel: unsupported temporal depth k=%d", k);
+    }
+    if (err == cudaSuccess) err = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    if (err != cudaSuccess) GOL_FAIL("occupancy query failed: %s", cudaGetErrorString(err));
+    *ctas = per_sm * sms;
+    return 0;
+}
+
+int gol_launch_persistent(const GolDomainDev *d_doms, const GolPersist &pp, int k, int ctas, CUstream_st *stream)
+{
+    void *args[] = {(void *)&d_doms, (void *)&pp};
+    const void *fn = nullptr;
+    switch (k) {
+    case 1: fn = (const void *)life_persistent_kernel<1>; break;
+    case 2: fn = (const void *)life_persistent_kernel<2>; break;
+    case 4: fn = (const void *)life_persistent_kernel<4>; break;
+    case 8: fn = (const void *)life_persistent_kernel<8>; break;
+    default: GOL_FAIL("persistent kernel: unsupported temporal depth k=%d", k);
+    }
+    // cooperative launch: the runtime guarantees that all CTAs are resident at once, which the
+    // item-to-item waits rely on
+    cudaError_t err = cudaLaunchCooperativeKernel(fn, dim3((unsigned)ctas), dim3(kWarps * 32), args, 0, stream);
+    if (err != cudaSuccess) GOL_FAIL("life_persistent_kernel<k=%d> launch failed: %s", k, cudaGetErrorString(err));
     return 0;
 }
 
