@@ -19,7 +19,7 @@ CPP_SRCS  := csrc/host_util.cpp
 OBJS      := $(CU_SRCS:csrc/%.cu=$(BUILD)/%.o) $(CPP_SRCS:csrc/%.cpp=$(BUILD)/%.o)
 HDRS      := include/gol_b200.h csrc/gol_internal.h csrc/life_rule.h
 
-all: $(LIB) bin/gol bin/gol-generate
+all: $(LIB) bin/gol bin/gol-generate bin/gol-intpeak
 
 $(BUILD)/%.o: csrc/%.cu $(HDRS)
 	@mkdir -p $(BUILD)
@@ -42,6 +42,10 @@ bin/gol-generate: csrc/generate_main.cpp $(LIB)
 	@mkdir -p bin
 	$(CXX) $(CXXFLAGS) $< -o $@ -L. -lgolb200 -Wl,-rpath,'$$ORIGIN/..' -Wl,-rpath,'$$ORIGIN'
 
+bin/gol-intpeak: csrc/int_peak.cu
+	@mkdir -p bin
+	$(NVCC) $(ARCH) -O3 -std=c++17 -lineinfo $< -o $@
+
 # the reference's make targets: same binary, different default variant, written to ./a.out
 game mpi collective async openmp cuda: $(LIB)
 	$(CXX) $(CXXFLAGS) -DGOL_DEFAULT_VARIANT='"$@"' csrc/cli_main.cpp -o a.out -L. -lgolb200 -Wl,-rpath,'$$ORIGIN'
@@ -50,6 +54,6 @@ oracle:
 	$(MAKE) -C baseline ref_serial
 
 clean:
-	rm -rf $(BUILD) $(LIB) bin/gol bin/gol-generate a.out
+	rm -rf $(BUILD) $(LIB) bin/gol bin/gol-generate bin/gol-intpeak a.out
 
 .PHONY: all lib game mpi collective async openmp cuda oracle clean

@@ -185,6 +185,8 @@ int upload_domains(gol_engine *e)
         D.rec_tables = e->d_rec_tables;
         D.proc_count = e->P;
         D.num_domains = e->ndom;
+        D.mul2 = 2;
+        D.mul4 = 4;
         for (int d = 0; d < GOL_NDIR; ++d) {
             const int ngid = neighbor_gid(e, ld.gid, d);
             if (ngid == ld.gid) D.self_mask |= 1u << d;

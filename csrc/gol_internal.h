@@ -74,7 +74,7 @@ struct GolScratch {            // per-domain device scratch (zero between launch
     unsigned int alive;        // OR of final-level cells
     unsigned int diff;         // OR of final-level (old ^ new)
     unsigned int error;        // sticky: flag-wait timeout etc.
-    unsigned int border_done;  // border work items finished in the current launch
+    unsigned int border_done[2];  // border work items finished, per epoch parity (two epochs can be in flight)
 };
 
 struct GolDomainDev {
@@ -91,6 +91,7 @@ struct GolDomainDev {
     unsigned long long **rec_tables;   // device array [proc_count]
     int32_t proc_count, num_domains;
     uint32_t self_mask;        // bit d set: the neighbour in direction d is this domain itself (torus wrap)
+    uint32_t mul2, mul4;       // the constants 2 and 4, kept opaque to ptxas so that shifts stay IMADs (FMA pipe)
 };
 
 struct GolLaunch {

@@ -1,0 +1,118 @@
+// Integer-pipe micro-benchmark for the roofline denominator ("the LOP3/INT32
+// peak is not in MEASURED_PEAKS.json and must be measured before quoting roofline fractions").
+// Measures sustained warp-instructions per clock per SM for LOP3, SHF (funnel shift), the
+// LOP3+SHF mix of the generation kernel (10:2), IMAD and SHFL, with 8 independent chains per
+// thread and full occupancy.  Prints one JSON object.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstdlib>
+
+#define CHECK(x)                                                                           \
+    do {                                                                                   \
+        cudaError_t e_ = (x);                                                              \
+        if (e_ != cudaSuccess) {                                                           \
+            fprintf(stderr, "CUDA error %s at line %d\n", cudaGetErrorString(e_), __LINE__); \
+            exit(1);                                                                       \
+        }                                                                                  \
+    } while (0)
+
+constexpr int kIters = 4096;
+constexpr int kChains = 8;
+
+template <int MODE>
+__global__ void __launch_bounds__(256) pipe_kernel(unsigned *out, unsigned seed)
+{
+    unsigned v[kChains];
+#pragma unroll
+    for (int j = 0; j < kChains; ++j) v[j] = seed * (threadIdx.x + 1) + j * 0x9E3779B9u;
+    unsigned a = seed ^ 0x55555555u, b = seed * 3u + 1u;
+    for (int i = 0; i < kIters; ++i) {
+#pragma unroll
+        for (int j = 0; j < kChains; ++j) {
+            if (MODE == 0) {  // LOP3
+                asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(v[j]) : "r"(a), "r"(b));
+            } else if (MODE == 1) {  // SHF
+                asm volatile("shf.l.wrap.b32 %0, %1, %0, 1;" : "+r"(v[j]) : "r"(a));
+            } else if (MODE == 2) {  // IMAD
+                asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(v[j]) : "r"(a), "r"(b));
+            } else if (MODE == 3) {  // SHFL
+                v[j] = __shfl_up_sync(0xffffffffu, v[j], 1);
+            } else if (MODE == 5) {  // IMAD.HI
+                asm volatile("mad.hi.u32 %0, %0, %1, %2;" : "+r"(v[j]) : "r"(a), "r"(b));
+            } else if (MODE == 6) {  // IMAD.WIDE (64-bit product, both halves consumed)
+                unsigned lo, hi;
+                asm volatile("{ .reg .b64 t; mul.wide.u32 t, %2, %3; mov.b64 {%0, %1}, t; }" : "=r"(lo), "=r"(hi) : "r"(v[j]), "r"(a));
+                v[j] = lo + hi;
+            } else if (MODE == 7) {  // 5 LOP3 + 1 IMAD: the mix with the shifts moved to the FMA pipe
+                asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(v[j]) : "r"(a), "r"(b));
+                asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(v[j]) : "r"(a), "r"(b));
+                asm volatile("lop3.b32 %0, %0, %1, %2, 0xE8;" : "+r"(v[j]) : "r"(a), "r"(b));
+                asm volatile("lop3.b32 %0, %0, %1, %2, 0x14;" : "+r"(v[j]) : "r"(a), "r"(b));
+                asm volatile("lop3.b32 %0, %0, %1, %2, 0x42;" : "+r"(v[j]) : "r"(a), "r"(b));
+                asm volatile("lop3.b32 %0, %0, %1, %2, 0xEA;" : "+r"(v[j]) : "r"(a), "r"(b));
+            } else if (MODE == 4) {  // kernel mix: 5 LOP3 + 1 SHF per chain step (= 10:2)
+                asm volatile("shf.l.wrap.b32 %0, %1, %0, 1;" : "+r"(v[j]) : "r"(a));
+                asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(v[j]) : "r"(a), "r"(b));
+                asm volatile("lop3.b32 %0, %0, %1, %2, 0xE8;" : "+r"(v[j]) : "r"(a), "r"(b));
+                asm volatile("lop3.b32 %0, %0, %1, %2, 0x14;" : "+r"(v[j]) : "r"(a), "r"(b));
+                asm volatile("lop3.b32 %0, %0, %1, %2, 0x42;" : "+r"(v[j]) : "r"(a), "r"(b));
+                asm volatile("lop3.b32 %0, %0, %1, %2, 0xEA;" : "+r"(v[j]) : "r"(a), "r"(b));
+            }
+        }
+    }
+    unsigned r = 0;
+#pragma unroll
+    for (int j = 0; j < kChains; ++j) r ^= v[j];
+    if (r == 0x12345678u) out[0] = r;  // never true in practice; keeps the chains alive
+}
+
+template <int MODE>
+double run(int sms, int clock_khz, double *ms_out)
+{
+    unsigned *d;
+    CHECK(cudaMalloc(&d, 4));
+    const int blocks = sms * 8;  // 8 x 256 threads = 64 warps per SM
+    cudaEvent_t e0, e1;
+    CHECK(cudaEventCreate(&e0));
+    CHECK(cudaEventCreate(&e1));
+    for (int w = 0; w < 3; ++w) pipe_kernel<MODE><<<blocks, 256>>>(d, 12345u + w);
+    CHECK(cudaEventRecord(e0));
+    const int reps = 5;
+    for (int r = 0; r < reps; ++r) pipe_kernel<MODE><<<blocks, 256>>>(d, 777u + r);
+    CHECK(cudaEventRecord(e1));
+    CHECK(cudaEventSynchronize(e1));
+    float ms;
+    CHECK(cudaEventElapsedTime(&ms, e0, e1));
+    const int per_step = (MODE == 4 || MODE == 7) ? 6 : (MODE == 6 ? 2 : 1);
+    const double warp_instr = (double)reps * blocks * 8.0 * kIters * kChains * per_step;
+    const double cycles = ms * 1e-3 * clock_khz * 1e3;
+    *ms_out = ms / reps;
+    CHECK(cudaFree(d));
+    return warp_instr / cycles / sms;  // warp-instructions per clock per SM
+}
+
+int main()
+{
+    cudaDeviceProp p;
+    CHECK(cudaGetDeviceProperties(&p, 0));
+    int clock_khz = 0;
+    CHECK(cudaDeviceGetAttribute(&clock_khz, cudaDevAttrClockRate, 0));
+    double ms[8];
+    const double lop3 = run<0>(p.multiProcessorCount, clock_khz, &ms[0]);
+    const double shf = run<1>(p.multiProcessorCount, clock_khz, &ms[1]);
+    const double imad = run<2>(p.multiProcessorCount, clock_khz, &ms[2]);
+    const double shfl = run<3>(p.multiProcessorCount, clock_khz, &ms[3]);
+    const double mix = run<4>(p.multiProcessorCount, clock_khz, &ms[4]);
+    const double imadhi = run<5>(p.multiProcessorCount, clock_khz, &ms[5]);
+    const double imadwide = run<6>(p.multiProcessorCount, clock_khz, &ms[6]);
+    const double mix_imad = run<7>(p.multiProcessorCount, clock_khz, &ms[7]);
+    // the generation kernel needs 12 ALU-pipe warp-instructions per 32 lanes x 32 cells
+    const double cells_per_s = mix * p.multiProcessorCount * (clock_khz * 1e3) * 1024.0 / 12.0;
+    printf("{\"gpu\": \"%s\", \"sms\": %d, \"clock_mhz_nominal_max\": %.0f, "
+           "\"warp_instr_per_clk_per_sm\": {\"lop3\": %.3f, \"shf\": %.3f, \"imad\": %.3f, \"shfl\": %.3f, \"lop3_shf_mix_10_2\": %.3f, \"imad_hi\": %.3f, \"imad_wide_plus_iadd\": %.3f, \"lop3_imad_mix_10_2\": %.3f}, "
+           "\"note\": \"rates assume the nominal max SM clock; 2.0 = 64 lanes/clk/SM\", "
+           "\"int_roofline_cell_updates_per_s_at_12_alu_ops_per_32_cells\": %.4g}\n",
+           p.name, p.multiProcessorCount, clock_khz / 1e3, lop3, shf, imad, shfl, mix, imadhi, imadwide, mix_imad, cells_per_s);
+    return 0;
+}

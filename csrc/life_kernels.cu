@@ -252,9 +252,12 @@ __device__ __forceinline__ void border_item_done(const GolDomainDev &D, const Go
     __threadfence_system();  // my pushes are visible system-wide before the count / the flags
     __syncwarp();
     if (lane == 0) {
-        const unsigned prev = atomicAdd(&D.scratch->border_done, 1u);
+        // In the persistent kernel border items of two consecutive epochs can be in flight (never
+        // more: an item of epoch e+2 needs the neighbours' flags of e+1, which need ours of e).
+        unsigned int *cnt = &D.scratch->border_done[lp.seq & 1u];
+        const unsigned prev = atomicAdd(cnt, 1u);
         if (prev == (unsigned)nborder - 1) {
-            D.scratch->border_done = 0;
+            *cnt = 0;
             __threadfence_system();
             for (int d = 0; d < GOL_NDIR; ++d) st_release_sys(D.nb[d].flag, lp.seq);
         }
@@ -304,6 +307,32 @@ __device__ __forceinline__ void stg_u32(uint32_t *p, uint32_t a)
     asm volatile("st.global.u32 [%0], %1;" ::"l"(p), "r"(a) : "memory");
 }
 
+// One-sided formulation (experiment, off by default): all three neighbour columns are taken from LEFT shifts,
+//   C = row word, A = C*2 + carry (cell x-1 at bit x), B = C*4 + carry (cell x-2 at bit x),
+// so the sums for cell x-1 appear at bit x and every level moves the picture one bit to the
+// left; the K bits are shifted back once per epoch.  Multiplying by 2 and 4 and adding the
+// carry is ONE full-rate IMAD each on the FMA pipe (the carries are IMAD.HI), which leaves the
+// ALU pipe with exactly the 10 LOP3 of the adder instead of 10 LOP3 + 2 SHF.  The multipliers
+// come from memory so that ptxas cannot turn them back into shifts.
+// Measured on B200 (16384^2, K=8): 12.04 us/generation against 10.24 for the funnel-shift form:
+// IMAD.HI issues at half rate (bin/gol-intpeak: 0.99 vs 1.98 warp-instr/clk/SM) and lengthens the
+// per-level dependency chain, which costs more than the two SHF it saves.
+#ifndef GOL_ONE_SIDED
+#define GOL_ONE_SIDED 0
+#endif
+__device__ __forceinline__ uint32_t mul_hi(uint32_t a, uint32_t b)
+{
+    uint32_t d;
+    asm("mul.hi.u32 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+    return d;
+}
+__device__ __forceinline__ uint32_t mad_lo(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
 struct MarchArgs {
     const uint32_t *in;   // padded input buffer (global)
     uint32_t *out;        // padded output buffer (global)
@@ -312,18 +341,31 @@ struct MarchArgs {
     int y0, y1;           // output rows [y0, y1)
     uint32_t keep[kWL];   // per-word ownership / tail mask of this lane
     int mode;             // 1 plain vector load, 2 composed ragged tail, 0 nothing to load
+    uint32_t two, four;   // run-time 2 and 4 (see GOL_ONE_SIDED)
 };
 
 // One warp streams rows [y0-K, y1+K) of generation g through K register-resident levels and
 // writes rows [y0, y1) of generation g+K.  FAST: every lane does a plain vector load and a
 // (predicated) vector store - true for all strips except the ragged right edge of a row.
+// Skewed pipeline (experiment, off by default): level t consumes the row level t-1 produced in the PREVIOUS step, so
+// the K levels of one step are independent instruction streams (ILP = K x 2 words per thread)
+// instead of one serial chain of K levels.  Costs K-1 extra drain steps per chunk and one
+// pending row per level.  Measured on B200 (16384^2, K=8): 11.00 us/generation against 10.24 - the
+// kernel is ALU-throughput bound, not latency bound, so the extra ILP buys nothing and the drain
+// steps cost 7 %.
+#ifndef GOL_SKEW
+#define GOL_SKEW 0
+#endif
+
 template <int K, bool FLAGS, bool FAST>
 __device__ __forceinline__ void march(const MarchArgs &A, uint32_t &flag_alive, uint32_t &flag_diff)
 {
+    constexpr int LAG = GOL_SKEW ? 2 * K - 1 : K;  // a step that consumes level-0 row r emits row r - LAG
     const int pitch = A.pitch;
     const bool store_all = (A.keep[0] & A.keep[1]) == 0xffffffffu;
     const bool store_any = (A.keep[0] | A.keep[1]) != 0u;
-    const int rbeg = A.y0 - K, rend = A.y1 + K;  // level-0 rows consumed: [rbeg, rend)
+    const int rbeg = A.y0 - K, rload_end = A.y1 + K;  // level-0 rows consumed: [rbeg, rload_end)
+    const int rend = A.y1 + LAG;                      // steps: r in [rbeg, rend)
     const uint32_t *pin = A.in + (int64_t)(rbeg + G) * pitch + GOL_GHOST_WORDS32;  // row being loaded
     uint32_t *pout = A.out + (int64_t)(A.y0 + G) * pitch + GOL_GHOST_WORDS32 + A.vi;
 
@@ -346,66 +388,120 @@ __device__ __forceinline__ void march(const MarchArgs &A, uint32_t &flag_alive, 
         pin += pitch;
     };
 
-    uint32_t h0[K][2][kWL], h1[K][2][kWL], ctr[K][kWL];
+    uint32_t h0[K][2][kWL], h1[K][2][kWL], ctr[K][kWL], pend[K][kWL];
 #pragma unroll
     for (int t = 0; t < K; ++t)
 #pragma unroll
         for (int j = 0; j < kWL; ++j) {
             h0[t][0][j] = h0[t][1][j] = h1[t][0][j] = h1[t][1][j] = 0;
             ctr[t][j] = 0;
+            pend[t][j] = 0;
         }
     uint32_t acc_a[kWL] = {0, 0}, acc_d[kWL] = {0, 0};
 
     // two rows of prefetch in flight
-    uint32_t cur[kWL], q0[kWL], q1[kWL];
+    uint32_t q0[kWL], q1[kWL];
     load_row(q0);
-    if (rbeg + 1 < rend) load_row(q1);
+    if (rbeg + 1 < rload_end) load_row(q1);
     else { q1[0] = q0[0]; q1[1] = q0[1]; }
 
-    auto step = [&](int r, auto par_tag) {
+    // One level: consumes row `x` of generation g+t, updates the level's 3-row window and returns
+    // the row of generation g+t+1 that sits one row above x.
+    auto level = [&](auto t_tag, auto par_tag, const uint32_t(&x)[kWL], uint32_t(&out)[kWL], bool flags_ok) {
+        constexpr int t = decltype(t_tag)::value;
         constexpr int PAR = decltype(par_tag)::value;
+#if GOL_ONE_SIDED
+        uint32_t c4[kWL], c2[kWL];  // carries out of each word: its top two bits / top bit
 #pragma unroll
-        for (int j = 0; j < kWL; ++j) { cur[j] = q0[j]; q0[j] = q1[j]; }
-        if (r + 2 < rend) load_row(q1);
+        for (int j = 0; j < kWL; ++j) {
+            c4[j] = mul_hi(x[j], A.four);
+            c2[j] = mul_hi(x[j], A.two);
+        }
+        const uint32_t in4 = __shfl_up_sync(0xffffffffu, c4[kWL - 1], 1);
+        const uint32_t in2 = __shfl_up_sync(0xffffffffu, c2[kWL - 1], 1);
+#else
+        const uint32_t left = __shfl_up_sync(0xffffffffu, x[kWL - 1], 1);
+        const uint32_t right = __shfl_down_sync(0xffffffffu, x[0], 1);
+#endif
 #pragma unroll
-        for (int t = 0; t < K; ++t) {
-            // cur = row (r - t) of generation g+t
-            const uint32_t left = __shfl_up_sync(0xffffffffu, cur[kWL - 1], 1);
-            const uint32_t right = __shfl_down_sync(0xffffffffu, cur[0], 1);
-            uint32_t nw_[kWL];
+        for (int j = 0; j < kWL; ++j) {
+#if GOL_ONE_SIDED
+            const uint32_t nL = mad_lo(x[j], A.four, j ? c4[j - 1] : in4);  // cell x-2 at bit x
+            const uint32_t nC = mad_lo(x[j], A.two, j ? c2[j - 1] : in2);   // cell x-1 at bit x (centre)
+            const uint32_t nR = x[j];
+#else
+            const uint32_t nL = shl1_in(j ? x[j - 1] : left, x[j]);
+            const uint32_t nC = x[j];
+            const uint32_t nR = shr1_in(x[j], j < kWL - 1 ? x[j + 1] : right);
+#endif
+            const uint32_t s0 = xor3(nL, nC, nR);
+            const uint32_t s1 = maj3(nL, nC, nR);
+            // window: two rows up (slot PAR), one row up (slot PAR^1, centre ctr[t]) and this row
+            const uint32_t v = life_rule(h0[t][PAR][j], h1[t][PAR][j], h0[t][PAR ^ 1][j], h1[t][PAR ^ 1][j], s0, s1,
+                                         ctr[t][j]);
+            h0[t][PAR][j] = s0;
+            h1[t][PAR][j] = s1;
+            if (FLAGS && t == K - 1 && flags_ok) {
+                acc_a[j] |= v;
+                acc_d[j] = lop3<0xF6>(acc_d[j], ctr[t][j], v);  // acc | (old ^ new)
+            }
+            ctr[t][j] = nC;
+            out[j] = v;
+        }
+    };
+
+    auto step = [&](int r, auto par_tag) {
+        uint32_t x0[kWL], fin[kWL];
+#pragma unroll
+        for (int j = 0; j < kWL; ++j) { x0[j] = q0[j]; q0[j] = q1[j]; }
+        if (r + 2 < rload_end) load_row(q1);
+        const bool emit = r - LAG >= A.y0;
+#if GOL_SKEW
+        // descending: level t+1 has already consumed pend[t+1] when level t overwrites it
+        auto run = [&](auto self, auto t_tag) -> void {
+            constexpr int t = decltype(t_tag)::value;
+            uint32_t o[kWL];
+            if constexpr (t == 0) level(t_tag, par_tag, x0, o, emit);
+            else level(t_tag, par_tag, pend[t], o, emit);
 #pragma unroll
             for (int j = 0; j < kWL; ++j) {
-                const uint32_t pw = j ? cur[j - 1] : left;
-                const uint32_t nx = j < kWL - 1 ? cur[j + 1] : right;
-                const uint32_t L = shl1_in(pw, cur[j]);
-                const uint32_t R = shr1_in(cur[j], nx);
-                const uint32_t s0 = xor3(L, cur[j], R);
-                const uint32_t s1 = maj3(L, cur[j], R);
-                // rows r-t-2 (slot PAR), r-t-1 (slot PAR^1, centre ctr[t]) and r-t (s0,s1)
-                nw_[j] = life_rule(h0[t][PAR][j], h1[t][PAR][j], h0[t][PAR ^ 1][j], h1[t][PAR ^ 1][j], s0, s1,
-                                   ctr[t][j]);
-                h0[t][PAR][j] = s0;
-                h1[t][PAR][j] = s1;
-                if (FLAGS && t == K - 1 && r >= A.y0 + K) {
-                    acc_a[j] |= nw_[j];
-                    acc_d[j] = lop3<0xF6>(acc_d[j], ctr[t][j], nw_[j]);  // acc | (old ^ new)
-                }
-                ctr[t][j] = cur[j];
+                if constexpr (t == K - 1) fin[j] = o[j];
+                else pend[t + 1][j] = o[j];
             }
+            if constexpr (t > 0) self(self, std::integral_constant<int, t - 1>{});
+        };
+        run(run, std::integral_constant<int, K - 1>{});
+#else
+        auto run = [&](auto self, auto t_tag, const uint32_t(&x)[kWL]) -> void {
+            constexpr int t = decltype(t_tag)::value;
+            uint32_t o[kWL];
+            level(t_tag, par_tag, x, o, emit);
+            if constexpr (t == K - 1) {
 #pragma unroll
-            for (int j = 0; j < kWL; ++j) cur[j] = nw_[j];
+                for (int j = 0; j < kWL; ++j) fin[j] = o[j];
+            } else {
+                self(self, std::integral_constant<int, t + 1>{}, o);
+            }
+        };
+        run(run, std::integral_constant<int, 0>{}, x0);
+#endif
+#if GOL_ONE_SIDED
+        {   // the K levels moved the picture K bits to the left: shift it back
+            const uint32_t up = __shfl_down_sync(0xffffffffu, fin[0], 1);
+#pragma unroll
+            for (int j = 0; j < kWL; ++j) fin[j] = __funnelshift_r(fin[j], j < kWL - 1 ? fin[j + 1] : up, K);
         }
-        // cur = row (r - K) of generation g+K
-        if (r - K >= A.y0) {
+#endif
+        if (emit) {  // fin = row (r - LAG) of generation g+K
             if (FAST) {
-                if (store_all) stg_v2(pout, cur[0], cur[1]);
+                if (store_all) stg_v2(pout, fin[0], fin[1]);
             } else if (store_any) {
                 if (store_all) {
-                    stg_v2(pout, cur[0], cur[1]);
+                    stg_v2(pout, fin[0], fin[1]);
                 } else {
 #pragma unroll
                     for (int j = 0; j < kWL; ++j)
-                        if (A.keep[j]) stg_u32(pout + j, cur[j] & A.keep[j]);
+                        if (A.keep[j]) stg_u32(pout + j, fin[j] & A.keep[j]);
                 }
             }
             pout += pitch;
@@ -420,6 +516,14 @@ __device__ __forceinline__ void march(const MarchArgs &A, uint32_t &flag_alive, 
     if (r < rend) step(r, std::integral_constant<int, 0>{});
 
     if (FLAGS) {
+#if GOL_ONE_SIDED
+        const uint32_t ua = __shfl_down_sync(0xffffffffu, acc_a[0], 1), ud = __shfl_down_sync(0xffffffffu, acc_d[0], 1);
+#pragma unroll
+        for (int j = 0; j < kWL; ++j) {
+            acc_a[j] = __funnelshift_r(acc_a[j], j < kWL - 1 ? acc_a[j + 1] : ua, K);
+            acc_d[j] = __funnelshift_r(acc_d[j], j < kWL - 1 ? acc_d[j + 1] : ud, K);
+        }
+#endif
         flag_alive = (acc_a[0] & A.keep[0]) | (acc_a[1] & A.keep[1]);
         flag_diff = (acc_d[0] & A.keep[0]) | (acc_d[1] & A.keep[1]);
     }
@@ -447,6 +551,7 @@ __device__ __forceinline__ void run_item(const GolDomainDev &D, const ItemCtx &c
     A.out = reinterpret_cast<uint32_t *>(__cvta_generic_to_global(D.buf[c.out_idx]));
     A.vi = strip_origin(strip, S, A.nw) - kWL + lane * kWL;
     A.y0 = y0; A.y1 = y1;
+    A.two = D.mul2; A.four = D.mul4;
     if (c.wait_seq && border) wait_neighbors(D, c.wait_seq, lane, c.skip_mask);
 
     // per-lane constants

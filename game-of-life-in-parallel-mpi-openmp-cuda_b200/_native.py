@@ -13,7 +13,7 @@ import subprocess
 import threading
 
 REPO_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB_PATH = os.path.join(REPO_ROOT, "libgolb200.so")
+LIB_PATH = os.environ.get("GOL_LIB") or os.path.join(REPO_ROOT, "libgolb200.so")  # GOL_LIB: kernel-variant experiments
 
 GHOST_ROWS = 16
 GHOST_WORDS32 = 4
