@@ -250,7 +250,11 @@ int launch_epoch(gol_engine *e, int k, int in, int out, bool flags, int rec_slot
     lp.out_idx = out;
     lp.wait_seq = multi(e) ? e->seq : 0;
     lp.seq = ++e->seq;
-    lp.signal = multi(e) ? 1 : 0;
+    static const int dbg = getenv("GOL_DEBUG_COMM") ? atoi(getenv("GOL_DEBUG_COMM")) : 0;  // timing experiments only
+    static const int force_signal = getenv("GOL_FORCE_SIGNAL") ? atoi(getenv("GOL_FORCE_SIGNAL")) : 0;
+    lp.signal = ((multi(e) || (force_signal & 1)) ? 1 : 0) | (dbg << 8);
+    if (force_signal & 2) lp.wait_seq = e->seq - 1;
+    if (dbg & 4) lp.wait_seq = 0;
     lp.rec_slot = flags ? rec_slot : -1;
     lp.rec_seq = rec_seq;
     GOL_TRY(gol_launch_strip(e->d_doms, e->per_proc, lp, k, flags ? 1 : 0, 0, e->stream));

@@ -113,77 +113,114 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys64(const unsigned lo
 // ---------------------------------------------------------------- border push
 // Copies the border rows / columns of rows [y0,y1) of buffer `o` owned by `strip` into the
 // ghost zones of the 8 neighbours.  Executed by one warp; reads data this warp wrote earlier.
-__device__ void push_borders(const GolDomainDev &D, int o, int strip, int y0, int y1, int lane)
+__device__ void push_borders(const GolDomainDev &D, int o, int strip, int y0, int y1, int lane, int dbg = 0)
 {
     const int H = D.H, nw = D.nw32, pitch = D.pitch32;
     const uint32_t *src = D.buf[o];
     const int lo = strip_origin(strip, D.strips, nw), hi = min(nw, lo + kVW);
+    const int npairs = (hi - lo) >> 1;  // uint2 elements per row owned by this strip (<= 30)
 
-    // rows -> north / south neighbours' ghost rows
-    for (int pass = 0; pass < 2; ++pass) {
-        const int dir = pass;  // 0 = N, 1 = S
+    // rows -> north / south neighbours' ghost rows.  All loads of a batch are issued before the
+    // first store, so a batch costs one memory round trip instead of one per row.
+    for (int pass = 0; pass < 2 && !(dbg & 2); ++pass) {
         const int ya = pass == 0 ? y0 : max(y0, H - G);
         const int yb = pass == 0 ? min(y1, G) : y1;
         if (ya >= yb) continue;
-        const GolNeighbor &nb = D.nb[dir];
-        for (int y = ya; y < yb; ++y) {
-            const int drow = pass == 0 ? (G + nb.H + y) : (G + y - H);
-            const uint32_t *s = src + (int64_t)(y + G) * pitch + GOL_GHOST_WORDS32;
-            uint32_t *d = nb.buf[o] + (int64_t)drow * nb.pitch32 + GOL_GHOST_WORDS32;
-            for (int i = lo + 2 * lane; i < hi; i += 64)
-                *reinterpret_cast<uint2 *>(d + i) = *reinterpret_cast<const uint2 *>(s + i);
+        const GolNeighbor &nb = D.nb[pass];  // 0 = N, 1 = S
+        const int total = (yb - ya) * npairs;
+        const int drow0 = pass == 0 ? (G + nb.H) : (G - H);
+        for (int base = 0; base < total; base += 32 * 8) {
+            uint2 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int e = base + u * 32 + lane;
+                if (e < total) {
+                    const int row = e / npairs, col = e - row * npairs;
+                    v[u] = *reinterpret_cast<const uint2 *>(src + (int64_t)(ya + row + G) * pitch + GOL_GHOST_WORDS32 + lo + 2 * col);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int e = base + u * 32 + lane;
+                if (e < total) {
+                    const int row = e / npairs, col = e - row * npairs;
+                    *reinterpret_cast<uint2 *>(nb.buf[o] + (int64_t)(drow0 + ya + row) * nb.pitch32 + GOL_GHOST_WORDS32 + lo + 2 * col) = v[u];
+                }
+            }
         }
     }
 
     const bool first = strip == 0, last = strip == D.strips - 1;
-    if (!first && !last) return;
+    if ((!first && !last) || (dbg & 1)) return;
     const int W_cells = D.nwf32 * 32 + D.rem;
-    for (int y = y0 + lane; y < y1; y += 32) {
-        const uint32_t *s = src + (int64_t)(y + G) * pitch + GOL_GHOST_WORDS32;
-        if (first) {
-            // my first cells -> west neighbours' right ghost slot, pre-shifted by their width % 64
-            const uint32_t w0 = s[0], w1 = s[1], w2 = s[2], w3 = s[3];
-            for (int v = 0; v < 3; ++v) {  // W, NW, SW
-                int dir, drow;
-                if (v == 0) { dir = 2; drow = G + y; }
-                else if (v == 1) { if (y >= G) continue; dir = 4; drow = G + D.nb[4].H + y; }
-                else { if (y < H - G) continue; dir = 6; drow = G + y - H; }
-                const GolNeighbor &nb = D.nb[dir];
-                const int sh = nb.rem, ws = sh >> 5, bs = sh & 31;
-                uint32_t in[4] = {w0, w1, w2, w3}, outw[4];
+    const int ob = W_cells - 128, wi0 = ob >> 5, bo = ob & 31;  // east: my last 128 cells start at word wi0, bit bo
+    constexpr int RB = 4;  // rows per lane and batch
+    for (int yb0 = y0; yb0 < y1; yb0 += 32 * RB) {
+        uint32_t wv[RB][4], ev[RB][5];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    uint32_t val = 0;
-                    const int a = j - ws;
-                    if (a >= 0) val = in[a] << bs;
-                    if (bs && a - 1 >= 0) val |= in[a - 1] >> (32 - bs);
-                    outw[j] = val;
+        for (int u = 0; u < RB; ++u) {
+            const int y = yb0 + u * 32 + lane;
+            if (y < y1) {
+                const uint32_t *s = src + (int64_t)(y + G) * pitch + GOL_GHOST_WORDS32;
+                if (first) {
+                    const uint4 q = *reinterpret_cast<const uint4 *>(s);
+                    wv[u][0] = q.x; wv[u][1] = q.y; wv[u][2] = q.z; wv[u][3] = q.w;
                 }
-                uint32_t *d = nb.buf[o] + (int64_t)drow * nb.pitch32 + GOL_GHOST_WORDS32 + nb.nw32;
-                // slot is 8-byte aligned (nw32 is even): two 64-bit stores
-                *reinterpret_cast<uint2 *>(d) = make_uint2(outw[0], outw[1]);
-                *reinterpret_cast<uint2 *>(d + 2) = make_uint2(outw[2], outw[3]);
+                if (last) {
+#pragma unroll
+                    for (int j = 0; j < 5; ++j) ev[u][j] = (wi0 + j < nw) ? s[wi0 + j] : 0u;
+                }
             }
         }
-        if (last) {
-            // my last 128 cells -> east neighbours' left ghost slot
-            uint32_t outw[4];
-            const int ob = W_cells - 128;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int bp = ob + 32 * j, wi = bp >> 5, bo = bp & 31;
-                uint32_t val = s[wi] >> bo;
-                if (bo && wi + 1 < nw) val |= s[wi + 1] << (32 - bo);
-                outw[j] = val;
+        for (int u = 0; u < RB; ++u) {
+            const int y = yb0 + u * 32 + lane;
+            if (y >= y1) continue;
+            if (first) {
+                // my first cells -> west neighbours' right ghost slot, pre-shifted by their width % 64
+                for (int v = 0; v < 3; ++v) {  // W, NW, SW
+                    int dir, drow;
+                    if (v == 0) { dir = 2; drow = G + y; }
+                    else if (v == 1) { if (y >= G) continue; dir = 4; drow = G + D.nb[4].H + y; }
+                    else { if (y < H - G) continue; dir = 6; drow = G + y - H; }
+                    const GolNeighbor &nb = D.nb[dir];
+                    const int sh = nb.rem;
+                    uint32_t outw[4];
+                    if (sh == 0) {
+                        outw[0] = wv[u][0]; outw[1] = wv[u][1]; outw[2] = wv[u][2]; outw[3] = wv[u][3];
+                    } else {
+                        const int ws = sh >> 5, bs = sh & 31;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            uint32_t val = 0;
+#pragma unroll
+                            for (int a = 0; a < 4; ++a) {
+                                if (a == j - ws) val |= wv[u][a] << bs;
+                                if (bs && a == j - ws - 1) val |= wv[u][a] >> (32 - bs);
+                            }
+                            outw[j] = val;
+                        }
+                    }
+                    uint32_t *d = nb.buf[o] + (int64_t)drow * nb.pitch32 + GOL_GHOST_WORDS32 + nb.nw32;
+                    // slot is 8-byte aligned (nw32 is even): two 64-bit stores
+                    *reinterpret_cast<uint2 *>(d) = make_uint2(outw[0], outw[1]);
+                    *reinterpret_cast<uint2 *>(d + 2) = make_uint2(outw[2], outw[3]);
+                }
             }
-            for (int v = 0; v < 3; ++v) {  // E, NE, SE
-                int dir, drow;
-                if (v == 0) { dir = 3; drow = G + y; }
-                else if (v == 1) { if (y >= G) continue; dir = 5; drow = G + D.nb[5].H + y; }
-                else { if (y < H - G) continue; dir = 7; drow = G + y - H; }
-                const GolNeighbor &nb = D.nb[dir];
-                uint32_t *d = nb.buf[o] + (int64_t)drow * nb.pitch32;
-                *reinterpret_cast<uint4 *>(d) = make_uint4(outw[0], outw[1], outw[2], outw[3]);
+            if (last) {
+                // my last 128 cells -> east neighbours' left ghost slot
+                uint32_t outw[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) outw[j] = bo ? ((ev[u][j] >> bo) | (ev[u][j + 1] << (32 - bo))) : ev[u][j];
+                for (int v = 0; v < 3; ++v) {  // E, NE, SE
+                    int dir, drow;
+                    if (v == 0) { dir = 3; drow = G + y; }
+                    else if (v == 1) { if (y >= G) continue; dir = 5; drow = G + D.nb[5].H + y; }
+                    else { if (y < H - G) continue; dir = 7; drow = G + y - H; }
+                    const GolNeighbor &nb = D.nb[dir];
+                    uint32_t *d = nb.buf[o] + (int64_t)drow * nb.pitch32;
+                    *reinterpret_cast<uint4 *>(d) = make_uint4(outw[0], outw[1], outw[2], outw[3]);
+                }
             }
         }
     }
@@ -249,7 +286,12 @@ __device__ __forceinline__ bool decode_item(const ItemMap &m, int item, int &str
 // Called by every border warp after its pushes: the last one publishes the epoch flags.
 __device__ __forceinline__ void border_item_done(const GolDomainDev &D, const GolLaunch &lp, int nborder, int lane)
 {
-    __threadfence_system();  // my pushes are visible system-wide before the count / the flags
+    // Release pattern with one system-scope fence per epoch instead of one per border warp: every
+    // border warp orders its pushes before its count at GPU scope; the warp that completes the
+    // count issues the (cumulative) system-scope fence before it publishes the flags, which
+    // carries all counted warps' pushes with it (PTX memory model: causality order is transitive
+    // over the gpu-scope atomic and the sys-scope release).
+    __threadfence();
     __syncwarp();
     if (lane == 0) {
         // In the persistent kernel border items of two consecutive epochs can be in flight (never
@@ -586,8 +628,8 @@ __device__ __forceinline__ void run_item(const GolDomainDev &D, const ItemCtx &c
     }
     __syncwarp();
     if (border) {
-        push_borders(D, c.out_idx, strip, y0, y1, lane);
-        if (c.signal) {
+        push_borders(D, c.out_idx, strip, y0, y1, lane, c.signal >> 8);
+        if (c.signal & 1) {
             GolLaunch lp;
             lp.seq = c.seq;
             border_item_done(D, lp, im.nborder, lane);

@@ -26,6 +26,8 @@ ap.add_argument("--size", type=int, default=16384)
 ap.add_argument("--gens", type=int, default=256)
 ap.add_argument("--skip-check", action="store_true")
 ap.add_argument("--grid", default="")
+ap.add_argument("--width", type=int, default=0, help="global width override (strong scaling configs)")
+ap.add_argument("--height", type=int, default=0)
 a = ap.parse_args()
 
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
@@ -95,7 +97,7 @@ if not a.skip_check:
     log("[check] early-exit semantics identical to the serial loop on every rank")
 
 # weak-scaling timing: size x size cells per GPU
-W, H = C * a.size, R * a.size
+W, H = (a.width or C * a.size), (a.height or R * a.size)
 life = gol_b200.GameOfLife(W, H, grid=(R, C), device=local, similarity_frequency=3, gen_limit=1000)
 life.randomize(1)
 for rep in range(3):
