@@ -21,7 +21,34 @@ class ClockSampler:
         self._stop = threading.Event()
         self._thread = None
 
+    def _poll_nvml(self) -> bool:
+        """Fast path: NVML through nvidia-ml-py (one sample per ~2 ms instead of ~80 ms per nvidia-smi call)."""
+        try:
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.gpu)
+            mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+        except Exception:
+            return False
+        bits = {"hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown,
+                "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown,
+                "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap}
+        while not self._stop.is_set():
+            try:
+                sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
+                pw = nv.nvmlDeviceGetPowerUsage(h) / 1000.0
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                flags = ["Active" if (r & b) else "Not Active" for b in bits.values()]
+                self.samples.append([str(sm), str(mx), f"{pw:.1f}", hex(r)] + flags)
+            except Exception:
+                pass
+            self._stop.wait(min(self.period, 0.005))
+        return True
+
     def _poll(self):
+        if self._poll_nvml():
+            return
         while not self._stop.is_set():
             try:
                 out = subprocess.run(["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={_QUERY}",
@@ -33,8 +60,6 @@ class ClockSampler:
             self._stop.wait(self.period)
 
     def start(self):
-        if shutil.which("nvidia-smi") is None:
-            return self
         self._thread = threading.Thread(target=self._poll, daemon=True)
         self._thread.start()
         return self
@@ -53,8 +78,14 @@ class ClockSampler:
             for name, val in zip(names, s[4:8]):
                 if val.lower().startswith("active"):
                     reasons.add(name)
+        pw = []
+        for s in self.samples:
+            try:
+                pw.append(float(s[2]))
+            except ValueError:
+                pass
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(self.samples)}
+                "reasons": sorted(reasons), "samples": len(self.samples), "power_w_max": max(pw) if pw else None}
 
 
 class Timer:
