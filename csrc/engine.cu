@@ -76,6 +76,7 @@ struct gol_engine {
     unsigned long long *d_results = nullptr;  // [kMaxBatch + 1]
     unsigned long long *h_results = nullptr;  // pinned
     unsigned int *d_error = nullptr;
+    uint64_t *stage = nullptr;      // dense staging buffer for linear host<->device copies (largest local domain)
     int max_strips = 1;
     int64_t max_h = 1;
     int64_t items_cap = 0;          // per-domain capacity of the item flag array
@@ -93,7 +94,7 @@ struct gol_engine {
     int64_t launches = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_slot[2] = {nullptr, nullptr};
     double last_ms = 0.0;
     int kmax = 8, batch = 128;
 };
@@ -264,7 +265,7 @@ int launch_epoch(gol_engine *e, int k, int in, int out, bool flags, int rec_slot
 
 // Run n generations starting from e->cur as epochs of at most kmax; buffers `keep` is never
 // written.  With want_flags the last epoch publishes a record (rec slot/seq returned).
-int run_epochs(gol_engine *e, int64_t n, int keep, bool want_flags, bool per_gen_flags, int kcap)
+int run_epochs(gol_engine *e, int64_t n, int keep, bool want_flags, bool per_gen_flags, int kcap, int keep2 = -1)
 {
     // Output buffers rotate over the buffers that are neither the epoch's input, nor the
     // previous epoch's input (a neighbouring rank may still be reading it: flags are published
@@ -281,8 +282,8 @@ int run_epochs(gol_engine *e, int64_t n, int keep, bool want_flags, bool per_gen
         if (want_flags && count * kp == left) --count;
         int rot[3], nrot = 0;
         for (int i = 0; i < GOL_NBUF; ++i)
-            if (i != in && i != keep && i != e->prev_in && nrot < 3) rot[nrot++] = i;
-        if (e->prev_in >= 0 && e->prev_in != in && e->prev_in != keep && nrot < 3) rot[nrot++] = e->prev_in;  // written last
+            if (i != in && i != keep && i != keep2 && i != e->prev_in && nrot < 3) rot[nrot++] = i;
+        if (e->prev_in >= 0 && e->prev_in != in && e->prev_in != keep && e->prev_in != keep2 && nrot < 3) rot[nrot++] = e->prev_in;  // written last
         if (count >= 2 && kp <= 8 && nrot == 3) {
             if (!e->persist_ctas[kp]) GOL_TRY(gol_persistent_max_ctas(kp, e->cfg.device, &e->persist_ctas[kp]));
             GolLaunch g{};
@@ -319,7 +320,10 @@ int run_epochs(gol_engine *e, int64_t n, int keep, bool want_flags, bool per_gen
         }
         int out = -1;
         for (int i = 0; i < GOL_NBUF; ++i)
-            if (i != in && i != e->prev_in && i != keep) { out = i; break; }
+            if (i != in && i != e->prev_in && i != keep && i != keep2) { out = i; break; }
+        if (out < 0)  // prev_in is only a hazard between ranks that run ahead; never when it is the last choice
+            for (int i = 0; i < GOL_NBUF; ++i)
+                if (i != in && i != keep && i != keep2) { out = i; break; }
         const bool last = left - k == 0;
         const bool f = per_gen_flags || (want_flags && last);
         uint32_t rs = 0;
@@ -401,20 +405,45 @@ void resolve_exit(int64_t gen0, int n, const std::vector<int> &alive, const std:
     *reason = GOL_EXIT_LIMIT;
 }
 
+// Population for gol_result without any allocation on the run path: counts straight from the
+// padded buffers into a spare word of the result array.
 int fill_population(gol_engine *e, gol_result *res)
 {
-    uint64_t pop = 0;
-    GOL_TRY(gol_engine_population(e, &pop));
-    res->population = pop;
+    if (!e->fast) {
+        uint64_t pop = 0;
+        GOL_TRY(gol_engine_population(e, &pop));
+        res->population = pop;
+        return 0;
+    }
+    unsigned long long *d_count = e->d_results + kMaxBatch + 1;
+    GOL_CUDA(cudaMemsetAsync(d_count, 0, sizeof(unsigned long long), e->stream));
+    for (int i = 0; i < e->per_proc; ++i) {
+        const char *src = e->arena + e->arena_layout.buf_off[(size_t)i * GOL_NBUF + e->cur];
+        GOL_TRY(gol_launch_popcount_padded(reinterpret_cast<const uint32_t *>(src), e->local[(size_t)i].L, d_count, e->stream));
+        ++e->launches;
+    }
+    GOL_CUDA(cudaMemcpyAsync(&e->h_results[kMaxBatch], d_count, sizeof(unsigned long long), cudaMemcpyDeviceToHost, e->stream));
+    GOL_CUDA(cudaStreamSynchronize(e->stream));
+    res->population = e->h_results[kMaxBatch];
     return 0;
 }
 
 // ------------------------------------------------------------ strip-path run
+// Asynchronous read-back of one 8-byte flag word: device result slot -> pinned host slot, then an
+// event the host can wait on while the GPU already runs the next batch.
+int post_result(gol_engine *e, int slot)
+{
+    GOL_CUDA(cudaMemcpyAsync(&e->h_results[slot], e->d_results + slot, sizeof(unsigned long long), cudaMemcpyDeviceToHost,
+                             e->stream));
+    GOL_CUDA(cudaEventRecord(e->ev_slot[slot & 1], e->stream));
+    return 0;
+}
+
 int run_fast(gol_engine *e, gol_result *res)
 {
     const int limit = e->cfg.gen_limit, freq = e->cfg.similarity_frequency;
     GOL_CUDA(cudaEventRecord(e->ev0, e->stream));
-    // empty() of generation 0
+    // empty() of generation 0: launched, not waited for - batch 0 runs behind it
     {
         GolLaunch lp{};
         geometry(e, 1, &lp);
@@ -427,46 +456,74 @@ int run_fast(gol_engine *e, gol_result *res)
         lp.rec_seq = rs;
         GOL_TRY(gol_launch_scan_alive(e->d_doms, e->per_proc, lp, e->stream));
         ++e->launches;
-        GOL_TRY(gather_last(e, 0));
-        GOL_TRY(fetch_results(e, 1));
+        GOL_TRY(gather_last(e, 1));
+        GOL_TRY(post_result(e, 1));
     }
-    int generations = 0, reason = GOL_EXIT_LIMIT;
+    int generations = limit, reason = GOL_EXIT_LIMIT;
     int64_t computed = 0;
-    if (!(e->h_results[0] & 1ull)) {
-        generations = 0;
-        reason = GOL_EXIT_EMPTY;
-    } else {
-        int64_t gen = 0;
-        generations = limit;
-        while (gen < limit) {
+
+    // Batches are pipelined one deep: while batch b runs, the host looks at the flags of batch
+    // b-1 (or of generation 0).  Exits are fixed points, so the batch that was launched "too
+    // many" never changes the result; it only costs its run time when an exit is found.
+    struct Pending { bool valid; int slot; int64_t gen0; int n; int ckpt; } pend = {true, 1, -1, 0, -1};
+    int64_t gen = 0;
+    int prev_ckpt = -1;
+    bool done = false;
+    while (!done) {
+        Pending cur_batch = {false, 0, 0, 0, -1};
+        if (gen < limit) {
             const int n = (int)std::min<int64_t>(e->batch, limit - gen);
             const int ckpt = e->cur;
-            GOL_TRY(run_epochs(e, n, ckpt, true, false, e->kmax));
-            GOL_TRY(gather_last(e, 0));
-            GOL_TRY(fetch_results(e, 1));
+            const int slot = pend.slot ^ 1;
+            GOL_TRY(run_epochs(e, n, ckpt, true, false, e->kmax, prev_ckpt));
+            GOL_TRY(gather_last(e, slot));
+            GOL_TRY(post_result(e, slot));
             computed += n;
-            const bool alive_end = e->h_results[0] & 1ull, diff_end = e->h_results[0] & 2ull;
-            if (!alive_end || (freq > 0 && !diff_end)) {
-                // replay the batch one generation at a time from its untouched input
-                e->cur = ckpt;
-                GOL_TRY(run_epochs(e, n, ckpt, true, true, 1));
-                GOL_TRY(fetch_results(e, n));
-                computed += n;
-                std::vector<int> alive((size_t)n + 1), diff((size_t)n + 1);
+            cur_batch = {true, slot, gen, n, ckpt};
+        }
+        if (pend.valid) {
+            GOL_CUDA(cudaEventSynchronize(e->ev_slot[pend.slot & 1]));
+            const unsigned long long r = e->h_results[pend.slot];
+            const bool alive_end = r & 1ull, diff_end = r & 2ull;
+            if (pend.gen0 < 0) {  // generation 0
+                if (!alive_end) {
+                    generations = 0;
+                    reason = GOL_EXIT_EMPTY;
+                    done = true;
+                }
+            } else if (!alive_end || (freq > 0 && !diff_end)) {
+                // replay that batch one generation at a time from its untouched input
+                GOL_CUDA(cudaStreamSynchronize(e->stream));
+                e->cur = pend.ckpt;
+                GOL_TRY(run_epochs(e, pend.n, pend.ckpt, true, true, 1));
+                GOL_TRY(fetch_results(e, pend.n));
+                computed += pend.n;
+                std::vector<int> alive((size_t)pend.n + 1), diff((size_t)pend.n + 1);
                 alive[0] = 1;
                 diff[0] = 1;
-                for (int i = 1; i <= n; ++i) {
+                for (int i = 1; i <= pend.n; ++i) {
                     alive[(size_t)i] = (int)(e->h_results[i - 1] & 1ull);
                     diff[(size_t)i] = (int)((e->h_results[i - 1] >> 1) & 1ull);
                 }
-                resolve_exit(gen, n, alive, diff, limit, freq, &generations, &reason);
-                break;
+                resolve_exit(pend.gen0, pend.n, alive, diff, limit, freq, &generations, &reason);
+                done = true;
             }
-            gen += n;
         }
+        if (!cur_batch.valid) done = true;
+        if (cur_batch.valid) {
+            prev_ckpt = cur_batch.ckpt;
+            gen += cur_batch.n;
+        }
+        pend = cur_batch;
     }
     GOL_CUDA(cudaEventRecord(e->ev1, e->stream));
     GOL_CUDA(cudaEventSynchronize(e->ev1));
+    {
+        unsigned int err = 0;
+        GOL_CUDA(cudaMemcpy(&err, e->d_error, sizeof err, cudaMemcpyDeviceToHost));
+        if (err) GOL_FAIL("device-side wait timed out (code %u): a neighbouring rank stopped making progress", err);
+        GOL_TRY(check_device_errors(e));
+    }
     float ms = 0;
     GOL_CUDA(cudaEventElapsedTime(&ms, e->ev0, e->ev1));
     e->last_ms = ms;
@@ -586,12 +643,15 @@ void gol_engine_destroy(gol_engine *e)
     if (e->d_results) cudaFree(e->d_results);
     if (e->h_results) cudaFreeHost(e->h_results);
     if (e->d_error) cudaFree(e->d_error);
+    if (e->stage) cudaFree(e->stage);
     for (auto &d : e->dense)
         if (d) cudaFree(d);
     if (e->d_dflags) cudaFree(e->d_dflags);
     if (e->h_dflags) cudaFreeHost(e->h_dflags);
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
+    for (auto &ev : e->ev_slot)
+        if (ev) cudaEventDestroy(ev);
     if (e->own_stream && e->stream) cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -607,6 +667,8 @@ static int engine_create_impl(gol_engine *e)
     e->own_stream = true;
     GOL_CUDA(cudaEventCreate(&e->ev0));
     GOL_CUDA(cudaEventCreate(&e->ev1));
+    GOL_CUDA(cudaEventCreateWithFlags(&e->ev_slot[0], cudaEventDisableTiming));
+    GOL_CUDA(cudaEventCreateWithFlags(&e->ev_slot[1], cudaEventDisableTiming));
 
     if (!e->fast) {
         const size_t bytes = (size_t)(gol_div_up(cfg.width, 64) * cfg.height) * sizeof(uint64_t);
@@ -655,6 +717,11 @@ static int engine_create_impl(gol_engine *e)
     GOL_CUDA(cudaMallocHost(&e->h_results, sizeof(unsigned long long) * (kMaxBatch + 2)));
     GOL_CUDA(cudaMalloc(&e->d_error, 2 * sizeof(unsigned int)));   // [0] error word, [1] persistent work counter
     GOL_CUDA(cudaMemset(e->d_error, 0, 2 * sizeof(unsigned int)));
+    {
+        size_t stage_bytes = 0;
+        for (const LocalDomain &ld : e->local) stage_bytes = std::max(stage_bytes, (size_t)ld.L.nq * (size_t)ld.L.height * 8);
+        GOL_CUDA(cudaMalloc(&e->stage, stage_bytes));
+    }
     if (e->P == 1) {
         GOL_TRY(upload_domains(e));
         e->imported = true;
@@ -815,9 +882,19 @@ int gol_engine_load_packed(gol_engine *e, const uint64_t *host)
         const LocalDomain &ld = e->local[(size_t)i];
         char *dst = e->arena + e->arena_layout.buf_off[(size_t)i * GOL_NBUF + e->cur];
         GOL_CUDA(cudaMemsetAsync(dst, 0, (size_t)ld.L.buffer_words32 * 4, e->stream));
-        GOL_CUDA(cudaMemcpy2DAsync(dst + ((int64_t)G * ld.L.pitch32 + GOL_GHOST_WORDS32) * 4, (size_t)ld.L.pitch32 * 4,
-                                   host + ld.y0 * nqg + ld.x0 / 64, (size_t)nqg * 8, (size_t)ld.L.nq * 8,
-                                   (size_t)ld.L.height, cudaMemcpyHostToDevice, e->stream));
+        if (ld.L.nq == nqg && e->stage) {
+            // full-width domain: its rows are contiguous in the host grid - one linear DMA into the
+            // staging buffer (a strided 2-D copy of 2 KiB rows runs far below PCIe speed), then a
+            // kernel spreads the rows into the padded layout
+            GOL_CUDA(cudaMemcpyAsync(e->stage, host + ld.y0 * nqg, (size_t)ld.L.nq * (size_t)ld.L.height * 8,
+                                     cudaMemcpyHostToDevice, e->stream));
+            GOL_TRY(gol_launch_dense_to_padded(e->stage, ld.L.nq, 0, reinterpret_cast<uint32_t *>(dst), ld.L, e->stream));
+            ++e->launches;
+        } else {
+            GOL_CUDA(cudaMemcpy2DAsync(dst + ((int64_t)G * ld.L.pitch32 + GOL_GHOST_WORDS32) * 4, (size_t)ld.L.pitch32 * 4,
+                                       host + ld.y0 * nqg + ld.x0 / 64, (size_t)nqg * 8, (size_t)ld.L.nq * 8,
+                                       (size_t)ld.L.height, cudaMemcpyHostToDevice, e->stream));
+        }
     }
     GOL_CUDA(cudaStreamSynchronize(e->stream));
     return 0;

@@ -51,7 +51,8 @@ static inline uint64_t gol_hash64(uint64_t seed, uint64_t qx, uint64_t y)
 }
 
 // ------------------------------------------------------- device descriptors
-#define GOL_NBUF 4        // rotating padded buffers per domain (in/out + 2 checkpoints)
+#define GOL_NBUF 5        // padded buffers per domain: 3 rotating (in / out / previous in) + the checkpoints of
+                          // the batch being run and of the batch whose flags are still in flight
 #define GOL_NDIR 8
 // direction order: N, S, W, E, NW, NE, SW, SE  (dy,dx)
 static const int GOL_DIR_DY[8] = {-1, 1, 0, 0, -1, -1, 1, 1};
@@ -135,6 +136,7 @@ int gol_launch_scan_alive(const GolDomainDev *d_doms, int ndoms, const GolLaunch
 int gol_write_all(int fd, const char *buf, size_t len, int64_t offset, const char *path);
 int gol_launch_gather(unsigned long long *rec_table, int slot, int num_domains, uint32_t seq,
                       unsigned long long *d_result, unsigned int *d_error, CUstream_st *stream);
+int gol_launch_popcount_padded(const uint32_t *d_pad, const gol_layout &L, unsigned long long *d_count, CUstream_st *stream);
 int gol_launch_dense_to_padded(const uint64_t *d_dense, int64_t dense_pitch_q, int64_t qx0, uint32_t *d_pad,
                                const gol_layout &L, CUstream_st *stream);
 int gol_launch_padded_to_dense(const uint32_t *d_pad, const gol_layout &L, uint64_t *d_dense,

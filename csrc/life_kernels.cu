@@ -17,6 +17,7 @@
 //  dense kernels — generic 1-generation torus step for any size (tiny grids, PyTorch op).
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <type_traits>
 
 #include "gol_internal.h"
@@ -571,6 +572,10 @@ __device__ __forceinline__ void march(const MarchArgs &A, uint32_t &flag_alive, 
     }
 }
 
+#ifndef GOL_K8_MINBLOCKS
+#define GOL_K8_MINBLOCKS 3   // keeps the K=8 kernels (flagged variant included) at 3 CTAs = 12 warps per SM
+#endif
+
 struct ItemCtx {
     int in_idx, out_idx;
     uint32_t seq, wait_seq;
@@ -638,7 +643,7 @@ __device__ __forceinline__ void run_item(const GolDomainDev &D, const ItemCtx &c
 }
 
 template <int K, bool FLAGS>
-__global__ void __launch_bounds__(kWarps * 32) life_strip_kernel(const GolDomainDev *__restrict__ doms,
+__global__ void __launch_bounds__(kWarps * 32, K == 8 ? GOL_K8_MINBLOCKS : 1) life_strip_kernel(const GolDomainDev *__restrict__ doms,
                                                                  const GolLaunch lp)
 {
     const int dom_id = blockIdx.x / lp.ctas_per_domain;
@@ -867,6 +872,20 @@ __global__ void padded_to_dense_kernel(const uint32_t *__restrict__ pad, int H, 
     dense[(int64_t)y * dense_pitch_q + qx0 + q] = v;
 }
 
+// live cells of a padded domain buffer (interior only), added to *count
+__global__ void popcount_padded_kernel(const uint32_t *__restrict__ pad, int H, int nq, int pitch32,
+                                       unsigned long long *count)
+{
+    unsigned long long c = 0;
+    const int64_t total = (int64_t)H * nq;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t y = i / nq, q = i - y * nq;
+        c += __popcll(reinterpret_cast<const unsigned long long *>(pad + (y + G) * pitch32 + GOL_GHOST_WORDS32)[q]);
+    }
+    for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(count, c);
+}
+
 template <int K, bool FLAGS>
 cudaError_t launch_strip_t(const GolDomainDev *d, int grid, const GolLaunch &lp, cudaStream_t s)
 {
@@ -973,6 +992,16 @@ int gol_launch_gather(unsigned long long *rec_table, int slot, int num_domains, 
                                               d_result, d_error);
     cudaError_t err = cudaGetLastError();
     if (err != cudaSuccess) GOL_FAIL("gather_flags_kernel launch failed: %s", cudaGetErrorString(err));
+    return 0;
+}
+
+int gol_launch_popcount_padded(const uint32_t *d_pad, const gol_layout &L, unsigned long long *d_count, CUstream_st *stream)
+{
+    const int64_t total = (int64_t)L.height * L.nq;
+    const int blocks = (int)std::min<int64_t>(148 * 8, gol_div_up(total, 256));
+    popcount_padded_kernel<<<blocks, 256, 0, stream>>>(d_pad, (int)L.height, L.nq, L.pitch32, d_count);
+    cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess) GOL_FAIL("popcount_padded launch failed: %s", cudaGetErrorString(err));
     return 0;
 }
 
