@@ -191,3 +191,15 @@ def test_cli_matches_unmodified_reference(cuda_device, ref_serial, tmp_path):
     # fewer than three arguments: the C programs do nothing and print Finished (S:238-241)
     p = subprocess.run([exe, "10"], cwd=tmp_path, capture_output=True, text=True, check=True)
     assert p.stdout == "Finished\n"
+
+
+def test_end_to_end_case_with_persistent_kernel(cuda_device):
+    # scripts/sanitize_case.py walks every kernel of the library, including the opt-in persistent
+    # (dataflow) kernel, and checks each against the CPU oracle; it is also the case meant for
+    # compute-sanitizer (closed on this pool, so it is run plain here)
+    import sys
+    env = dict(os.environ, GOL_PERSISTENT="1")
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "sanitize_case.py")], capture_output=True,
+                       text=True, timeout=300, env=env)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    assert "sanitize case ok" in p.stdout
