@@ -30,7 +30,7 @@ $(BUILD)/%.o: csrc/%.cpp $(HDRS)
 	$(CXX) $(CXXFLAGS) -c $< -o $@
 
 $(LIB): $(OBJS)
-	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -Xlinker -soname=$(LIB)
+	$(NVCC) $(ARCH) -shared -o $@ $(OBJS) -Xlinker -soname=$(LIB) -ldl
 
 lib: $(LIB)
 

@@ -37,7 +37,7 @@ struct Options {
     std::string input, output, variant = GOL_DEFAULT_VARIANT, pbm;
     int gen_limit = GOL_DEFAULT_GEN_LIMIT;
     int sim_freq = GOL_DEFAULT_SIMILARITY_FREQUENCY;
-    int gpus = 1, ranks = 0, grid_r = 0, grid_c = 0, k = 0, batch = 0;
+    int gpus = 1, ranks = 0, grid_r = 0, grid_c = 0, k = 0, batch = 0, start_gen = 0;
     bool generic = false, lenient = false, no_write = false, stats = false, have_random = false;
     unsigned long long seed = 0;
 };
@@ -91,6 +91,7 @@ void usage()
             "  --grid RxC               domain decomposition (default: near-square for --gpus/--ranks)\n"
             "  --ranks X                number of domains (like mpiexec -n X); may exceed --gpus\n"
             "  --k K --batch B          temporal depth per launch / generations per flag check\n"
+            "  --start-generation G     resume: the input file is generation G of an earlier run\n"
             "  --generic                force the generic 1-generation kernel\n"
             "  --lenient                bytes other than 0/1 are dead cells instead of an error\n"
             "  --random SEED            ignore the input file, start from a seeded random grid\n"
@@ -122,6 +123,7 @@ int run_rank(const Options &opt, int rank, int nproc, Shared *sh)
     cfg.similarity_frequency = opt.sim_freq;
     cfg.k_max = opt.k;
     cfg.batch_gens = opt.batch;
+    cfg.start_generation = opt.start_gen;
     cfg.flags = opt.generic ? GOL_FLAG_FORCE_GENERIC : 0;
     gol_engine *eng = nullptr;
     if (gol_engine_create(&cfg, &eng)) {
@@ -255,6 +257,7 @@ int main(int argc, char **argv)
         else if (a == "--grid") { if (sscanf(next("--grid"), "%dx%d", &opt.grid_r, &opt.grid_c) != 2) { usage(); return EXIT_FAILURE; } }
         else if (a == "--k") opt.k = atoi(next("--k"));
         else if (a == "--batch") opt.batch = atoi(next("--batch"));
+        else if (a == "--start-generation") opt.start_gen = atoi(next("--start-generation"));
         else if (a == "--generic") opt.generic = true;
         else if (a == "--lenient") opt.lenient = true;
         else if (a == "--no-write") opt.no_write = true;

@@ -15,6 +15,7 @@
 // input buffer one generation at a time with per-generation flags, and the serial loop is
 // evaluated literally on those flags to obtain the exact "Generations:" value.
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 
 #include <algorithm>
 #include <cerrno>
@@ -27,6 +28,12 @@
 #include "gol_internal.h"
 
 namespace {
+
+// NVTX range for the timeline of a profiler (phases: load / prepare / batch / replay / store).
+struct NvtxRange {
+    explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+};
 
 constexpr int G = GOL_GHOST_ROWS;
 constexpr int kMaxBatch = 512;
@@ -461,17 +468,19 @@ int run_fast(gol_engine *e, gol_result *res)
     }
     int generations = limit, reason = GOL_EXIT_LIMIT;
     int64_t computed = 0;
+    const int64_t gen_start = e->cfg.start_generation;
 
     // Batches are pipelined one deep: while batch b runs, the host looks at the flags of batch
     // b-1 (or of generation 0).  Exits are fixed points, so the batch that was launched "too
     // many" never changes the result; it only costs its run time when an exit is found.
     struct Pending { bool valid; int slot; int64_t gen0; int n; int ckpt; } pend = {true, 1, -1, 0, -1};
-    int64_t gen = 0;
+    int64_t gen = gen_start;
     int prev_ckpt = -1;
     bool done = false;
     while (!done) {
         Pending cur_batch = {false, 0, 0, 0, -1};
         if (gen < limit) {
+            NvtxRange nv("gol batch");
             const int n = (int)std::min<int64_t>(e->batch, limit - gen);
             const int ckpt = e->cur;
             const int slot = pend.slot ^ 1;
@@ -487,12 +496,13 @@ int run_fast(gol_engine *e, gol_result *res)
             const bool alive_end = r & 1ull, diff_end = r & 2ull;
             if (pend.gen0 < 0) {  // generation 0
                 if (!alive_end) {
-                    generations = 0;
+                    generations = (int)gen_start;
                     reason = GOL_EXIT_EMPTY;
                     done = true;
                 }
             } else if (!alive_end || (freq > 0 && !diff_end)) {
                 // replay that batch one generation at a time from its untouched input
+                NvtxRange nv("gol exit replay");
                 GOL_CUDA(cudaStreamSynchronize(e->stream));
                 e->cur = pend.ckpt;
                 GOL_TRY(run_epochs(e, pend.n, pend.ckpt, true, true, 1));
@@ -557,7 +567,7 @@ int run_dense(gol_engine *e, gol_result *res)
     const int64_t W = e->cfg.width, H = e->cfg.height;
     GOL_CUDA(cudaEventRecord(e->ev0, e->stream));
     int generations = limit, reason = GOL_EXIT_LIMIT;
-    int64_t computed = 0, gen = 0;
+    int64_t computed = 0, gen = e->cfg.start_generation;
     bool known_alive = false;
     while (gen < limit) {
         const int n = (int)std::min<int64_t>(std::min(e->batch, kMaxBatch), limit - gen);
@@ -740,6 +750,8 @@ int gol_engine_create(const gol_config *cfg_in, gol_engine **out)
     if (cfg.proc_count < 1) cfg.proc_count = 1;
     if (cfg.gen_limit <= 0) cfg.gen_limit = GOL_DEFAULT_GEN_LIMIT;
     if (cfg.similarity_frequency < 0) cfg.similarity_frequency = GOL_DEFAULT_SIMILARITY_FREQUENCY;
+    if (cfg.start_generation < 0) cfg.start_generation = 0;
+    if (cfg.start_generation > cfg.gen_limit) cfg.start_generation = cfg.gen_limit;
     const int ndom = cfg.grid_rows * cfg.grid_cols;
     if (ndom % cfg.proc_count) GOL_FAIL("%d domains cannot be dealt evenly to %d processes", ndom, cfg.proc_count);
     if (cfg.proc_rank < 0 || cfg.proc_rank >= cfg.proc_count) GOL_FAIL("process rank %d out of range", cfg.proc_rank);
@@ -976,6 +988,7 @@ int gol_engine_download_packed(gol_engine *e, uint64_t *host)
 // gol_file_read_packed (host filter with the fgetc semantics) + gol_engine_load_packed.
 int gol_engine_load_text_file(gol_engine *e, const char *path, int strict)
 {
+    NvtxRange nv("gol load_text_file");
     GOL_CUDA(cudaSetDevice(e->cfg.device));
     const int64_t W = e->cfg.width, H = e->cfg.height;
     int fd = open(path, O_RDONLY);
@@ -1085,6 +1098,7 @@ int gol_engine_load_text_file(gol_engine *e, const char *path, int strict)
 
 int gol_engine_store_text_file(gol_engine *e, const char *path)
 {
+    NvtxRange nv("gol store_text_file");
     GOL_CUDA(cudaSetDevice(e->cfg.device));
     const int64_t W = e->cfg.width, H = e->cfg.height;
     int fd = open(path, O_WRONLY | O_CREAT, 0644);
@@ -1153,6 +1167,7 @@ int gol_engine_store_text_file(gol_engine *e, const char *path)
 // ------------------------------------------------------------------- driver
 int gol_engine_prepare(gol_engine *e)
 {
+    NvtxRange nv("gol prepare (first halo exchange)");
     GOL_CUDA(cudaSetDevice(e->cfg.device));
     GOL_TRY(check_ready(e, "gol_engine_prepare"));
     if (e->fast) {
@@ -1198,6 +1213,7 @@ int gol_engine_step(gol_engine *e, int64_t n)
 
 int gol_engine_run(gol_engine *e, gol_result *res)
 {
+    NvtxRange nv("gol run");
     GOL_CUDA(cudaSetDevice(e->cfg.device));
     GOL_TRY(check_ready(e, "gol_engine_run"));
     if (!e->prepared) GOL_TRY(gol_engine_prepare(e));

@@ -44,7 +44,8 @@ class Config(C.Structure):
     _fields_ = [("width", C.c_int64), ("height", C.c_int64), ("grid_rows", C.c_int32),
                 ("grid_cols", C.c_int32), ("proc_rank", C.c_int32), ("proc_count", C.c_int32),
                 ("device", C.c_int32), ("gen_limit", C.c_int32), ("similarity_frequency", C.c_int32),
-                ("k_max", C.c_int32), ("batch_gens", C.c_int32), ("flags", C.c_uint32)]
+                ("k_max", C.c_int32), ("batch_gens", C.c_int32), ("flags", C.c_uint32),
+                ("start_generation", C.c_int32), ("reserved", C.c_int32)]
 
 
 _lock = threading.Lock()

@@ -45,6 +45,7 @@ class LifeConfig:
     k_max: int = 0                     # temporal blocking depth (0 = auto)
     batch_gens: int = 0                # generations between flag checks (0 = auto)
     force_generic: bool = False
+    start_generation: int = 0          # resume: the loaded grid is this generation (checkpoint/restart)
 
 
 class _DeviceBuffer:
@@ -91,6 +92,7 @@ class GameOfLife:
         nc.k_max = cfg.k_max
         nc.batch_gens = cfg.batch_gens
         nc.flags = N.FLAG_FORCE_GENERIC if cfg.force_generic else 0
+        nc.start_generation = cfg.start_generation
         handle = C.c_void_p()
         N.check(lib.gol_engine_create(C.byref(nc), C.byref(handle)), "gol_engine_create")
         self._h = handle

@@ -170,6 +170,10 @@ typedef struct gol_config {
     int32_t k_max;              /* temporal-blocking depth per launch (0 = auto)     */
     int32_t batch_gens;         /* generations between flag checks (0 = auto)        */
     uint32_t flags;
+    int32_t start_generation;   /* resume support: the loaded grid is generation g (default 0); the   */
+                                /* loop continues with evolve ordinal g+1, so the similarity phase     */
+                                /* and the reported Generations carry on where a previous run stopped  */
+    int32_t reserved;
 } gol_config;
 
 void gol_config_default(gol_config *cfg, int64_t width, int64_t height);

@@ -203,3 +203,43 @@ def test_end_to_end_case_with_persistent_kernel(cuda_device):
                        text=True, timeout=300, env=env)
     assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
     assert "sanitize case ok" in p.stdout
+
+
+def test_resume_from_checkpoint_file(cuda_device, tmp_path):
+    # output format == input format (README.md:61-63 of the reference), so a run can be resumed from
+    # its output; start_generation restores the generation count and the similarity phase
+    from gol_b200.ops import cpu
+    from gol_b200.utils import patterns
+    w, h = 192, 48
+    cells = patterns.grid_with(w, h, ("rpentomino", 90, 20), ("glider", 10, 10))
+    start = cpu.pack(cells)
+    want, wres = cpu.run(start, w, gen_limit=400)
+    for stop in (1, 4, 5, 97):
+        a = make(w, h, gen_limit=stop, similarity_frequency=0)
+        a.load_packed(start)
+        assert a.run().generations == stop
+        ck = tmp_path / f"ck{stop}.txt"
+        a.save(str(ck))
+        a.close()
+        b = make(w, h, gen_limit=400, start_generation=stop)
+        b.load_file(str(ck))
+        res = b.run()
+        assert (res.generations, res.exit_reason) == (wres.generations, wres.exit_reason), (stop, res, wres)
+        assert np.array_equal(b.packed_numpy(), want)
+        b.close()
+
+
+def test_property_random_shapes_and_decompositions(cuda_device):
+    # k temporally blocked generations == k single generations for random sizes / depths / grids
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=25, deadline=None)
+    @given(st.integers(128, 2600), st.integers(16, 260), st.sampled_from([1, 2, 4, 8, 16]),
+           st.sampled_from([(1, 1), (1, 2), (2, 1), (2, 2), (1, 3), (3, 1)]), st.integers(1, 40), st.integers(0, 2 ** 31))
+    def prop(w, h, k, grid, n, seed):
+        r, c = grid
+        if w // c < 192 or h // r < 16:
+            grid = (1, 1)
+        check_steps(w, h, [n], seed=seed, k_max=k, grid=grid)
+
+    prop()
