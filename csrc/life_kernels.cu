@@ -399,6 +399,9 @@ struct MarchArgs {
 #ifndef GOL_SKEW
 #define GOL_SKEW 0
 #endif
+#ifndef GOL_WARM_SPLIT
+#define GOL_WARM_SPLIT 1   // prune the inactive levels of the pipeline fill (see march)
+#endif
 
 template <int K, bool FLAGS, bool FAST>
 __device__ __forceinline__ void march(const MarchArgs &A, uint32_t &flag_alive, uint32_t &flag_diff)
@@ -493,12 +496,17 @@ __device__ __forceinline__ void march(const MarchArgs &A, uint32_t &flag_alive, 
         }
     };
 
-    auto step = [&](int r, auto par_tag) {
+    // WARM steps are the pipeline fill: level t only starts once its first valid input row
+    // (y0-K+t) has come down the chain, i.e. at step r = rbeg + 2t.  The levels of a step form a
+    // chain, so the inactive ones are a suffix and a warm step simply stops early; nothing is
+    // emitted yet.  This removes K(K-1) of the 2K*K fill/drain level-steps of a chunk.
+    auto step = [&](int r, auto par_tag, auto warm_tag) {
+        constexpr bool WARM = decltype(warm_tag)::value;
         uint32_t x0[kWL], fin[kWL];
 #pragma unroll
-        for (int j = 0; j < kWL; ++j) { x0[j] = q0[j]; q0[j] = q1[j]; }
+        for (int j = 0; j < kWL; ++j) { x0[j] = q0[j]; q0[j] = q1[j]; fin[j] = 0; }
         if (r + 2 < rload_end) load_row(q1);
-        const bool emit = r - LAG >= A.y0;
+        const bool emit = !WARM && r - LAG >= A.y0;
 #if GOL_SKEW
         // descending: level t+1 has already consumed pend[t+1] when level t overwrites it
         auto run = [&](auto self, auto t_tag) -> void {
@@ -523,40 +531,50 @@ __device__ __forceinline__ void march(const MarchArgs &A, uint32_t &flag_alive, 
 #pragma unroll
                 for (int j = 0; j < kWL; ++j) fin[j] = o[j];
             } else {
-                self(self, std::integral_constant<int, t + 1>{}, o);
+                if (!WARM || r >= rbeg + 2 * (t + 1)) self(self, std::integral_constant<int, t + 1>{}, o);
             }
         };
         run(run, std::integral_constant<int, 0>{}, x0);
 #endif
+        if constexpr (!WARM) {
 #if GOL_ONE_SIDED
-        {   // the K levels moved the picture K bits to the left: shift it back
-            const uint32_t up = __shfl_down_sync(0xffffffffu, fin[0], 1);
+            {   // the K levels moved the picture K bits to the left: shift it back
+                const uint32_t up = __shfl_down_sync(0xffffffffu, fin[0], 1);
 #pragma unroll
-            for (int j = 0; j < kWL; ++j) fin[j] = __funnelshift_r(fin[j], j < kWL - 1 ? fin[j + 1] : up, K);
-        }
-#endif
-        if (emit) {  // fin = row (r - LAG) of generation g+K
-            if (FAST) {
-                if (store_all) stg_v2(pout, fin[0], fin[1]);
-            } else if (store_any) {
-                if (store_all) {
-                    stg_v2(pout, fin[0], fin[1]);
-                } else {
-#pragma unroll
-                    for (int j = 0; j < kWL; ++j)
-                        if (A.keep[j]) stg_u32(pout + j, fin[j] & A.keep[j]);
-                }
+                for (int j = 0; j < kWL; ++j) fin[j] = __funnelshift_r(fin[j], j < kWL - 1 ? fin[j + 1] : up, K);
             }
-            pout += pitch;
+#endif
+            if (emit) {  // fin = row (r - LAG) of generation g+K
+                if (FAST) {
+                    if (store_all) stg_v2(pout, fin[0], fin[1]);
+                } else if (store_any) {
+                    if (store_all) {
+                        stg_v2(pout, fin[0], fin[1]);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < kWL; ++j)
+                            if (A.keep[j]) stg_u32(pout + j, fin[j] & A.keep[j]);
+                    }
+                }
+                pout += pitch;
+            }
         }
     };
 
     int r = rbeg;
-    for (; r + 1 < rend; r += 2) {
-        step(r, std::integral_constant<int, 0>{});
-        step(r + 1, std::integral_constant<int, 1>{});
+#if !GOL_SKEW && GOL_WARM_SPLIT
+    // fill: 2K-2 steps (always even, so the window parity stays aligned); chunks are >= 1 row, so
+    // the loop below still has at least 3 steps left
+    for (; r < rbeg + 2 * K - 2; r += 2) {
+        step(r, std::integral_constant<int, 0>{}, std::true_type{});
+        step(r + 1, std::integral_constant<int, 1>{}, std::true_type{});
     }
-    if (r < rend) step(r, std::integral_constant<int, 0>{});
+#endif
+    for (; r + 1 < rend; r += 2) {
+        step(r, std::integral_constant<int, 0>{}, std::false_type{});
+        step(r + 1, std::integral_constant<int, 1>{}, std::false_type{});
+    }
+    if (r < rend) step(r, std::integral_constant<int, 0>{}, std::false_type{});
 
     if (FLAGS) {
 #if GOL_ONE_SIDED
