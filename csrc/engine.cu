@@ -88,7 +88,9 @@ struct gol_engine {
     int64_t max_h = 1;
     int64_t items_cap = 0;          // per-domain capacity of the item flag array
     bool use_persistent = false;    // GOL_PERSISTENT=1: one dataflow launch per batch instead of one per epoch
-    int persist_ctas[9] = {0};      // max co-resident CTAs of the persistent kernel per k (0 = not queried)
+    int persist_ctas[9] = {0};
+    int tuned_rows[17] = {0};       // measured best chunk height per temporal depth (0 = not tuned yet)
+    bool autotune = true;           // GOL_AUTOTUNE=0 disables the one-off geometry timing      // max co-resident CTAs of the persistent kernel per k (0 = not queried)
 
     // dense path (tiny grids, single domain)
     uint64_t *dense[3] = {nullptr, nullptr, nullptr};
@@ -101,7 +103,7 @@ struct gol_engine {
     int64_t launches = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_slot[2] = {nullptr, nullptr};
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_slot[2] = {nullptr, nullptr}, ev_tune[2] = {nullptr, nullptr};
     double last_ms = 0.0;
     int kmax = 8, batch = 128;
 };
@@ -226,6 +228,13 @@ int upload_domains(gol_engine *e)
 void geometry(const gol_engine *e, int k, GolLaunch *lp, int resident_warps_per_sm = 0)
 {
     static const int env_warps = getenv("GOL_WARPS_PER_SM") ? atoi(getenv("GOL_WARPS_PER_SM")) : 0;
+    if (!env_warps && !resident_warps_per_sm && k <= 16 && e->tuned_rows[k] > 0) {
+        const int64_t rows = e->tuned_rows[k], chunks = gol_div_up(e->max_h, rows);
+        lp->chunk_rows = (int32_t)rows;
+        lp->chunks = (int32_t)chunks;
+        lp->ctas_per_domain = (int32_t)gol_div_up(chunks * e->max_strips, 4);
+        return;
+    }
     const int warps_per_sm = env_warps ? env_warps : (resident_warps_per_sm ? resident_warps_per_sm : 16);
     const int64_t target_items = (int64_t)e->num_sms * warps_per_sm / std::max(1, e->per_proc);
     // classic launches round up (a few CTAs more than slots is harmless); the persistent kernel
@@ -267,6 +276,63 @@ int launch_epoch(gol_engine *e, int k, int in, int out, bool flags, int rec_slot
     lp.rec_seq = rec_seq;
     GOL_TRY(gol_launch_strip(e->d_doms, e->per_proc, lp, k, flags ? 1 : 0, 0, e->stream));
     ++e->launches;
+    return 0;
+}
+
+// One-off geometry tuning for temporal depth k: the run time of an epoch is far from monotonic in
+// the chunk height (apron rows per chunk against wave quantisation of the CTA scheduler), so a
+// handful of candidate heights is timed on the real grid - pushes and flags switched off, output
+// into a free buffer that the next real epoch overwrites - and the fastest is kept.
+int autotune_geometry(gol_engine *e, int k, int in, int scratch)
+{
+    if (k > 16 || e->tuned_rows[k] || e->max_h < 256) return 0;
+    std::vector<int> cands;
+    for (int w = 10; w <= 26; ++w) {
+        const int64_t target = (int64_t)e->num_sms * w / std::max(1, e->per_proc);
+        int64_t chunks = std::max<int64_t>(1, gol_div_up(target, e->max_strips));
+        int64_t rows = std::max<int64_t>(gol_div_up(e->max_h, chunks), std::min<int64_t>(e->max_h, std::max(8, 4 * k)));
+        if (std::find(cands.begin(), cands.end(), (int)rows) == cands.end()) cands.push_back((int)rows);
+    }
+    float best = 1e30f;
+    int best_rows = 0;
+    auto time_rows = [&](int rows, float *ms_out) -> int {
+        GolLaunch lp{};
+        lp.chunk_rows = rows;
+        lp.chunks = (int32_t)gol_div_up(e->max_h, rows);
+        lp.ctas_per_domain = (int32_t)gol_div_up((int64_t)lp.chunks * e->max_strips, 4);
+        lp.in_idx = in;
+        lp.out_idx = scratch;
+        lp.seq = e->seq;
+        lp.wait_seq = 0;
+        lp.signal = 3 << 8;  // no pushes, no flags
+        lp.rec_slot = -1;
+        GOL_TRY(gol_launch_strip(e->d_doms, e->per_proc, lp, k, 0, 0, e->stream));
+        GOL_CUDA(cudaEventRecord(e->ev_tune[0], e->stream));
+        for (int i = 0; i < 3; ++i) GOL_TRY(gol_launch_strip(e->d_doms, e->per_proc, lp, k, 0, 0, e->stream));
+        GOL_CUDA(cudaEventRecord(e->ev_tune[1], e->stream));
+        GOL_CUDA(cudaEventSynchronize(e->ev_tune[1]));
+        e->launches += 4;
+        GOL_CUDA(cudaEventElapsedTime(ms_out, e->ev_tune[0], e->ev_tune[1]));
+        if (e->cfg.flags & GOL_FLAG_VERBOSE)
+            fprintf(stderr, "[gol autotune] k=%d chunk_rows=%d: %.2f us/epoch\n", k, rows, *ms_out * 1e3f / 3);
+        return 0;
+    };
+    for (int rows : cands) {
+        float ms = 0;
+        GOL_TRY(time_rows(rows, &ms));
+        if (ms < best) { best = ms; best_rows = rows; }
+    }
+    // local refinement around the coarse winner
+    const int centre = best_rows;
+    for (int d = -3; d <= 3; ++d) {
+        const int rows = centre + d;
+        if (d == 0 || rows < std::max(8, 2 * k) || rows > e->max_h) continue;
+        if (std::find(cands.begin(), cands.end(), rows) != cands.end()) continue;
+        float ms = 0;
+        GOL_TRY(time_rows(rows, &ms));
+        if (ms < best) { best = ms; best_rows = rows; }
+    }
+    e->tuned_rows[k] = best_rows;
     return 0;
 }
 
@@ -662,6 +728,8 @@ void gol_engine_destroy(gol_engine *e)
     if (e->ev1) cudaEventDestroy(e->ev1);
     for (auto &ev : e->ev_slot)
         if (ev) cudaEventDestroy(ev);
+    for (auto &ev : e->ev_tune)
+        if (ev) cudaEventDestroy(ev);
     if (e->own_stream && e->stream) cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -677,6 +745,8 @@ static int engine_create_impl(gol_engine *e)
     e->own_stream = true;
     GOL_CUDA(cudaEventCreate(&e->ev0));
     GOL_CUDA(cudaEventCreate(&e->ev1));
+    GOL_CUDA(cudaEventCreate(&e->ev_tune[0]));
+    GOL_CUDA(cudaEventCreate(&e->ev_tune[1]));
     GOL_CUDA(cudaEventCreateWithFlags(&e->ev_slot[0], cudaEventDisableTiming));
     GOL_CUDA(cudaEventCreateWithFlags(&e->ev_slot[1], cudaEventDisableTiming));
 
@@ -715,6 +785,8 @@ static int engine_create_impl(gol_engine *e)
     }
     e->items_cap = (int64_t)e->max_strips * gol_div_up(e->max_h, 8) + 64;
     if (const char *v = getenv("GOL_PERSISTENT")) e->use_persistent = atoi(v) != 0;
+    if (const char *v = getenv("GOL_AUTOTUNE")) e->autotune = atoi(v) != 0;
+    if (getenv("GOL_VERBOSE")) e->cfg.flags |= GOL_FLAG_VERBOSE;
     GOL_TRY(build_arena_layout(e, e->rank, &e->arena_layout));
     GOL_CUDA(cudaMalloc(&e->arena, (size_t)e->arena_layout.total));
     GOL_CUDA(cudaMemset(e->arena, 0, (size_t)e->arena_layout.total));
@@ -1181,6 +1253,9 @@ int gol_engine_prepare(gol_engine *e)
         lp.rec_slot = -1;
         GOL_TRY(gol_launch_halo(e->d_doms, e->per_proc, lp, 0, e->stream));
         ++e->launches;
+        // geometry tuning belongs to set-up, not to the timed generation loop
+        if (e->autotune && e->kmax >= 2 && !e->tuned_rows[e->kmax])
+            GOL_TRY(autotune_geometry(e, e->kmax, e->cur, (e->cur + 1) % GOL_NBUF));
     }
     e->prepared = true;
     return 0;
