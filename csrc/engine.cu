@@ -252,6 +252,14 @@ void geometry(const gol_engine *e, int k, GolLaunch *lp, int resident_warps_per_
 
 bool multi(const gol_engine *e) { return e->P > 1; }
 
+// largest temporal depth the strip kernel is instantiated for that does not exceed cap
+int pick_depth(int64_t cap)
+{
+    if (cap >= 16) return 16;
+    if (cap >= 8) return 8;
+    return (int)std::max<int64_t>(1, cap);
+}
+
 int check_ready(gol_engine *e, const char *what)
 {
     if (e->P > 1 && !e->imported) GOL_FAIL("%s: multi-process engine used before gol_engine_ipc_import", what);
@@ -349,15 +357,14 @@ int run_epochs(gol_engine *e, int64_t n, int keep, bool want_flags, bool per_gen
     // Leading run of full-depth epochs: one persistent (dataflow) launch instead of one launch
     // per epoch.  The flagged last epoch of a batch and remainder epochs stay classic launches.
     if (!per_gen_flags && e->use_persistent) {
-        int kp = 1;
-        while (kp * 2 <= std::min<int64_t>(left, kcap)) kp *= 2;
+        const int kp = pick_depth(std::min<int64_t>(left, kcap));
         int64_t count = left / kp;
         if (want_flags && count * kp == left) --count;
         int rot[3], nrot = 0;
         for (int i = 0; i < GOL_NBUF; ++i)
             if (i != in && i != keep && i != keep2 && i != e->prev_in && nrot < 3) rot[nrot++] = i;
         if (e->prev_in >= 0 && e->prev_in != in && e->prev_in != keep && e->prev_in != keep2 && nrot < 3) rot[nrot++] = e->prev_in;  // written last
-        if (count >= 2 && kp <= 8 && nrot == 3) {
+        if (count >= 2 && (kp == 1 || kp == 2 || kp == 4 || kp == 8) && nrot == 3) {
             if (!e->persist_ctas[kp]) GOL_TRY(gol_persistent_max_ctas(kp, e->cfg.device, &e->persist_ctas[kp]));
             GolLaunch g{};
             geometry(e, kp, &g);
@@ -388,8 +395,7 @@ int run_epochs(gol_engine *e, int64_t n, int keep, bool want_flags, bool per_gen
     while (left > 0) {
         int k = 1;
         if (!per_gen_flags) {
-            const int cap = (int)std::min<int64_t>(left, kcap);
-            while (k * 2 <= cap) k *= 2;
+            k = pick_depth(std::min<int64_t>(left, kcap));
         }
         int out = -1;
         for (int i = 0; i < GOL_NBUF; ++i)
@@ -859,9 +865,7 @@ int gol_engine_create(const gol_config *cfg_in, gol_engine **out)
     e->fast = fast;
     e->kmax = cfg.k_max > 0 ? cfg.k_max : 8;
     if (e->kmax > GOL_GHOST_ROWS) e->kmax = GOL_GHOST_ROWS;
-    int kk = 1;
-    while (kk * 2 <= e->kmax) kk *= 2;
-    e->kmax = kk;
+    e->kmax = pick_depth(e->kmax);
     e->batch = cfg.batch_gens > 0 ? cfg.batch_gens : 128;
     if (e->batch > kMaxBatch) e->batch = kMaxBatch;
 

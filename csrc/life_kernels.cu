@@ -661,7 +661,7 @@ __device__ __forceinline__ void run_item(const GolDomainDev &D, const ItemCtx &c
 }
 
 template <int K, bool FLAGS>
-__global__ void __launch_bounds__(kWarps * 32, K == 8 ? GOL_K8_MINBLOCKS : 1) life_strip_kernel(const GolDomainDev *__restrict__ doms,
+__global__ void __launch_bounds__(kWarps * 32, K == 8 ? GOL_K8_MINBLOCKS : (K == 6 ? 4 : 1)) life_strip_kernel(const GolDomainDev *__restrict__ doms,
                                                                  const GolLaunch lp)
 {
     const int dom_id = blockIdx.x / lp.ctas_per_domain;
@@ -933,7 +933,11 @@ int gol_launch_strip(const GolDomainDev *d_doms, int ndoms, const GolLaunch &lp,
     switch (k) {
         GOL_CASE(1)
         GOL_CASE(2)
+        GOL_CASE(3)
         GOL_CASE(4)
+        GOL_CASE(5)
+        GOL_CASE(6)
+        GOL_CASE(7)
         GOL_CASE(8)
         GOL_CASE(16)
     default:
