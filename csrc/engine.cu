@@ -301,6 +301,20 @@ int autotune_geometry(gol_engine *e, int k, int in, int scratch)
         int64_t rows = std::max<int64_t>(gol_div_up(e->max_h, chunks), std::min<int64_t>(e->max_h, std::max(8, 4 * k)));
         if (std::find(cands.begin(), cands.end(), (int)rows) == cands.end()) cands.push_back((int)rows);
     }
+    // heights that fill the machine exactly: m full waves of resident CTAs, no partial last wave
+    int occ = 0;
+    if (gol_strip_ctas_per_sm(k, &occ) == 0 && occ > 0) {
+        const int64_t slots = (int64_t)e->num_sms * occ * 4 / std::max(1, e->per_proc);  // warps = work items
+        for (int m = 1; m <= 3; ++m) {
+            const int64_t chunks = m * slots / e->max_strips;
+            if (chunks < 1) continue;
+            for (int extra = 0; extra <= 1; ++extra) {
+                const int64_t rows = gol_div_up(e->max_h, chunks) + extra;
+                if (rows < std::max(8, 2 * k) || rows > e->max_h) continue;
+                if (std::find(cands.begin(), cands.end(), (int)rows) == cands.end()) cands.push_back((int)rows);
+            }
+        }
+    }
     float best = 1e30f;
     int best_rows = 0;
     auto time_rows = [&](int rows, float *ms_out) -> int {

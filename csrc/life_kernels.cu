@@ -954,6 +954,32 @@ static cudaError_t persistent_occupancy(int *ctas_per_sm)
     return cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, life_persistent_kernel<K>, kWarps * 32, 0);
 }
 
+template <int K>
+static cudaError_t strip_occupancy(int *ctas_per_sm)
+{
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, life_strip_kernel<K, false>, kWarps * 32, 0);
+}
+
+// resident CTAs per SM of the (unflagged) strip kernel for depth k
+int gol_strip_ctas_per_sm(int k, int *ctas_per_sm)
+{
+    cudaError_t err = cudaSuccess;
+    switch (k) {
+    case 1: err = strip_occupancy<1>(ctas_per_sm); break;
+    case 2: err = strip_occupancy<2>(ctas_per_sm); break;
+    case 3: err = strip_occupancy<3>(ctas_per_sm); break;
+    case 4: err = strip_occupancy<4>(ctas_per_sm); break;
+    case 5: err = strip_occupancy<5>(ctas_per_sm); break;
+    case 6: err = strip_occupancy<6>(ctas_per_sm); break;
+    case 7: err = strip_occupancy<7>(ctas_per_sm); break;
+    case 8: err = strip_occupancy<8>(ctas_per_sm); break;
+    case 16: err = strip_occupancy<16>(ctas_per_sm); break;
+    default: GOL_FAIL("unsupported temporal depth k=%d", k);
+    }
+    if (err != cudaSuccess) GOL_FAIL("occupancy query failed: %s", cudaGetErrorString(err));
+    return 0;
+}
+
 int gol_persistent_max_ctas(int k, int device, int *ctas)
 {
     int per_sm = 0, sms = 0;
