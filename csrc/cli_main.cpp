@@ -38,7 +38,7 @@ struct Options {
     int gen_limit = GOL_DEFAULT_GEN_LIMIT;
     int sim_freq = GOL_DEFAULT_SIMILARITY_FREQUENCY;
     int gpus = 1, ranks = 0, grid_r = 0, grid_c = 0, k = 0, batch = 0, start_gen = 0;
-    bool generic = false, lenient = false, no_write = false, stats = false, have_random = false;
+    bool generic = false, lenient = false, no_write = false, stats = false, have_random = false, show = false;
     unsigned long long seed = 0;
 };
 
@@ -96,6 +96,7 @@ void usage()
             "  --lenient                bytes other than 0/1 are dead cells instead of an error\n"
             "  --random SEED            ignore the input file, start from a seeded random grid\n"
             "  --pbm PATH               also dump the final grid as a PBM image (headless show())\n"
+            "  --show                   print the final grid with VT100 escape codes like the reference's show()\n"
             "  --no-write --stats\n");
 }
 
@@ -208,6 +209,19 @@ int run_rank(const Options &opt, int rank, int nproc, Shared *sh)
                     cells * (double)res.generations_computed / (loop_ms * 1e-3), pop, gol_engine_uses_fast_path(eng),
                     (long long)gol_engine_launch_count(eng));
         }
+        if (opt.show && nproc == 1) {
+            // the reference's show() (S:42-58, dead code there): VT100 reverse-video blocks on stdout
+            std::vector<uint64_t> packed((size_t)((opt.width + 63) / 64 * opt.height));
+            if (gol_engine_download_packed(eng, packed.data())) die(sh, "show");
+            const long long nq = (opt.width + 63) / 64;
+            printf("\033[H");
+            for (long long y = 0; y < opt.height; ++y) {
+                for (long long x = 0; x < opt.width; ++x)
+                    printf(((packed[(size_t)(y * nq + (x >> 6))] >> (x & 63)) & 1ull) ? "\033[07m  \033[m" : "  ");
+                printf("\033[E");
+            }
+            fflush(stdout);
+        }
         if (!opt.pbm.empty() && nproc == 1) {
             std::vector<uint64_t> packed((size_t)((opt.width + 63) / 64 * opt.height));
             if (gol_engine_download_packed(eng, packed.data()) || gol_write_pbm(opt.pbm.c_str(), packed.data(), opt.width, opt.height))
@@ -263,6 +277,7 @@ int main(int argc, char **argv)
         else if (a == "--no-write") opt.no_write = true;
         else if (a == "--stats") opt.stats = true;
         else if (a == "--pbm") opt.pbm = next("--pbm");
+        else if (a == "--show") opt.show = true;
         else if (a == "--random") { opt.have_random = true; opt.seed = strtoull(next("--random"), nullptr, 10); }
         else if (a == "--help") { usage(); return 0; }
         else { fprintf(stderr, "unknown option %s\n", a.c_str()); usage(); return EXIT_FAILURE; }

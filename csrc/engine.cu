@@ -282,7 +282,7 @@ int launch_epoch(gol_engine *e, int k, int in, int out, bool flags, int rec_slot
     if (dbg & 4) lp.wait_seq = 0;
     lp.rec_slot = flags ? rec_slot : -1;
     lp.rec_seq = rec_seq;
-    GOL_TRY(gol_launch_strip(e->d_doms, e->per_proc, lp, k, flags ? 1 : 0, 0, e->stream));
+    GOL_TRY(gol_launch_strip(e->d_doms, e->per_proc, lp, k, flags ? 1 : 0, e->stream));
     ++e->launches;
     return 0;
 }
@@ -328,9 +328,9 @@ int autotune_geometry(gol_engine *e, int k, int in, int scratch)
         lp.wait_seq = 0;
         lp.signal = 3 << 8;  // no pushes, no flags
         lp.rec_slot = -1;
-        GOL_TRY(gol_launch_strip(e->d_doms, e->per_proc, lp, k, 0, 0, e->stream));
+        GOL_TRY(gol_launch_strip(e->d_doms, e->per_proc, lp, k, 0, e->stream));
         GOL_CUDA(cudaEventRecord(e->ev_tune[0], e->stream));
-        for (int i = 0; i < 3; ++i) GOL_TRY(gol_launch_strip(e->d_doms, e->per_proc, lp, k, 0, 0, e->stream));
+        for (int i = 0; i < 3; ++i) GOL_TRY(gol_launch_strip(e->d_doms, e->per_proc, lp, k, 0, e->stream));
         GOL_CUDA(cudaEventRecord(e->ev_tune[1], e->stream));
         GOL_CUDA(cudaEventSynchronize(e->ev_tune[1]));
         e->launches += 4;
@@ -757,6 +757,14 @@ void gol_engine_destroy(gol_engine *e)
 static int engine_create_impl(gol_engine *e)
 {
     const gol_config &cfg = e->cfg;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) {
+        cudaGetLastError();
+        GOL_FAIL("no usable CUDA device (the engine has no CPU fallback; gol_cpu_run is the CPU path)");
+    }
+    if (cfg.device < 0 || cfg.device >= ndev)
+        GOL_FAIL("CUDA device %d requested but %d device(s) are visible (one process per GPU: the process count "
+                 "must not exceed the GPU count)", cfg.device, ndev);
     GOL_CUDA(cudaSetDevice(cfg.device));
     cudaDeviceProp prop;
     GOL_CUDA(cudaGetDeviceProperties(&prop, cfg.device));
@@ -1269,7 +1277,7 @@ int gol_engine_prepare(gol_engine *e)
         lp.seq = ++e->seq;
         lp.signal = multi(e) ? 1 : 0;
         lp.rec_slot = -1;
-        GOL_TRY(gol_launch_halo(e->d_doms, e->per_proc, lp, 0, e->stream));
+        GOL_TRY(gol_launch_halo(e->d_doms, e->per_proc, lp, e->stream));
         ++e->launches;
         // geometry tuning belongs to set-up, not to the timed generation loop
         if (e->autotune && e->kmax >= 2 && !e->tuned_rows[e->kmax])

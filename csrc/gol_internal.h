@@ -126,9 +126,8 @@ struct GolPersist {
 // (implemented in life_kernels.cu)
 struct CUstream_st;
 int gol_launch_strip(const GolDomainDev *d_doms, int ndoms, const GolLaunch &lp, int k, int want_flags,
-                     int max_items_per_domain, CUstream_st *stream);
-int gol_launch_halo(const GolDomainDev *d_doms, int ndoms, const GolLaunch &lp, int max_rows,
-                    CUstream_st *stream);
+                     CUstream_st *stream);
+int gol_launch_halo(const GolDomainDev *d_doms, int ndoms, const GolLaunch &lp, CUstream_st *stream);
 int gol_strip_geometry(int nw32, int *strips);
 int gol_persistent_max_ctas(int k, int device, int *ctas);
 int gol_strip_ctas_per_sm(int k, int *ctas_per_sm);
@@ -141,4 +140,4 @@ int gol_launch_popcount_padded(const uint32_t *d_pad, const gol_layout &L, unsig
 int gol_launch_dense_to_padded(const uint64_t *d_dense, int64_t dense_pitch_q, int64_t qx0, uint32_t *d_pad,
                                const gol_layout &L, CUstream_st *stream);
 int gol_launch_padded_to_dense(const uint32_t *d_pad, const gol_layout &L, uint64_t *d_dense,
-                               int64_t dense_pitch_q, int64_t qx0, int shift, CUstream_st *stream);
+                               int64_t dense_pitch_q, int64_t qx0, int unused, CUstream_st *stream);

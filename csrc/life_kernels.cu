@@ -920,9 +920,8 @@ int gol_strip_geometry(int nw32, int *strips)
 }
 
 int gol_launch_strip(const GolDomainDev *d_doms, int ndoms, const GolLaunch &lp, int k, int want_flags,
-                     int max_items_per_domain, CUstream_st *stream)
+                     CUstream_st *stream)
 {
-    (void)max_items_per_domain;
     const int grid = ndoms * lp.ctas_per_domain;
     cudaError_t err;
 #define GOL_CASE(KK)                                                                  \
@@ -1015,10 +1014,8 @@ int gol_launch_persistent(const GolDomainDev *d_doms, const GolPersist &pp, int 
     return 0;
 }
 
-int gol_launch_halo(const GolDomainDev *d_doms, int ndoms, const GolLaunch &lp, int max_rows,
-                    CUstream_st *stream)
+int gol_launch_halo(const GolDomainDev *d_doms, int ndoms, const GolLaunch &lp, CUstream_st *stream)
 {
-    (void)max_rows;
     halo_push_kernel<<<ndoms * lp.ctas_per_domain, kWarps * 32, 0, stream>>>(d_doms, lp);
     cudaError_t err = cudaGetLastError();
     if (err != cudaSuccess) GOL_FAIL("halo_push_kernel launch failed: %s", cudaGetErrorString(err));

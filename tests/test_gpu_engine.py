@@ -243,3 +243,22 @@ def test_property_random_shapes_and_decompositions(cuda_device):
         check_steps(w, h, [n], seed=seed, k_max=k, grid=grid)
 
     prop()
+
+
+def test_cli_one_process_per_gpu(cuda_device, tmp_path):
+    # forked ranks + shared-memory rendezvous + CUDA IPC (needs two GPUs; the driver's box has one or eight)
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs at least two GPUs")
+    from gol_b200.ops import cpu
+    n = 1024
+    inp = tmp_path / "in.txt"
+    cpu.random_text_file(str(inp), n, n, 44)
+    exe = os.path.join(ROOT, "bin", "gol")
+    subprocess.run([exe, str(n), str(n), str(inp), "--variant", "cuda", "--gen-limit", "100"], cwd=tmp_path, check=True,
+                   capture_output=True)
+    p = subprocess.run([exe, str(n), str(n), str(inp), "--variant", "collective", "--gpus", "2", "--gen-limit", "100"],
+                       cwd=tmp_path, check=True, capture_output=True, text=True)
+    assert "Generations:\t100\n" in p.stdout and p.stdout.count("Finished") == 2
+    assert (tmp_path / "collective_output.out").read_bytes() == (tmp_path / "cuda_output.out").read_bytes()
+    want = cpu.format_text(cpu.step(cpu.random_grid(n, n, 44), n, 100), n)
+    assert (tmp_path / "cuda_output.out").read_bytes() == want
