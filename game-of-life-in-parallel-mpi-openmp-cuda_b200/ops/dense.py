@@ -140,3 +140,19 @@ def population(packed: torch.Tensor, width: int) -> int:
         N.check(N.lib().gol_op_popcount_dense(packed.data_ptr(), width, packed.shape[0], c.data_ptr(), _stream()),
                 "population")
     return int(c.item())
+
+
+# ---------------------------------------------------------------- torch.library registration
+# The step is also registered as a PyTorch custom op (torch.ops.gol_b200.step_dense) with a fake
+# (meta) implementation, so it composes with code that traces or inspects ops; the kernel behind
+# it is the same hand-written CUDA kernel - there is no compiler on the hot path.
+try:
+    @torch.library.custom_op("gol_b200::step_dense", mutates_args=(), device_types="cuda")
+    def step_dense_op(packed: torch.Tensor, width: int) -> torch.Tensor:
+        return step(packed, width)
+
+    @step_dense_op.register_fake
+    def _(packed, width):
+        return torch.empty_like(packed)
+except Exception:  # pragma: no cover - very old torch without torch.library.custom_op
+    step_dense_op = None

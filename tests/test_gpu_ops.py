@@ -73,3 +73,37 @@ def test_parse_format_random_match_cpu(cuda_device):
     bad[2, 1025] = ord("0")
     with pytest.raises(Exception, match="newline"):
         dense.parse_text(bad, 1025, 5)
+
+
+def test_custom_op_and_module(cuda_device):
+    from gol_b200.models import LifeStep
+    from gol_b200.ops import dense
+    g = torch.Generator(device="cpu").manual_seed(5)
+    cells = (torch.rand((3, 40, 70), generator=g) < 0.4).to(torch.uint8).to(cuda_device)
+    out = LifeStep(generations=2)(cells)
+    for i in range(3):
+        assert torch.equal(out[i], conv_oracle(conv_oracle(cells[i])))
+    packed = dense.pack_cells(cells[0].contiguous())
+    assert torch.equal(torch.ops.gol_b200.step_dense(packed, 70), dense.step(packed, 70))
+
+
+def test_bench_contract(cuda_device):
+    # the JSON line the driver parses (small grid so that the test stays short)
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    p = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--steps", "2", "--warmup", "3", "--size", "2048",
+                        "--gens", "200"], capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stderr[-2000:]
+    lines = [l for l in p.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    for key in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+                "vs_baseline", "dtype", "data", "config", "e2e", "gpu_launches", "clocks"):
+        assert key in d, key
+    assert d["n_gpus"] == 1 and d["steps"] == 2 and d["warmup"] == 3 and d["higher_is_better"] is True
+    assert d["value"] > 0 and d["e2e"]["value"] > 0 and d["e2e"]["value"] < d["value"] * 1.001
+    assert d["e2e"]["h2d_bytes_per_step"] == 2048 * 2048 // 8 and d["gpu_launches"] > 0
+    assert d["config"]["generations_reported"] == 200 and d["config"]["fast_path"] is True
