@@ -446,10 +446,12 @@ __device__ __forceinline__ void march(const MarchArgs &A, uint32_t &flag_alive, 
     uint32_t acc_a[kWL] = {0, 0}, acc_d[kWL] = {0, 0};
 
     // two rows of prefetch in flight
-    uint32_t q0[kWL], q1[kWL];
-    load_row(q0);
-    if (rbeg + 1 < rload_end) load_row(q1);
-    else { q1[0] = q0[0]; q1[1] = q0[1]; }
+    // q[p] holds the row for the next step of parity p: a row is requested two full steps before it
+    // is touched again (no queue shifting - a move out of a register with a load in flight stalls)
+    uint32_t q[2][kWL];
+    load_row(q[0]);
+    if (rbeg + 1 < rload_end) load_row(q[1]);
+    else { q[1][0] = q[0][0]; q[1][1] = q[0][1]; }
 
     // One level: consumes row `x` of generation g+t, updates the level's 3-row window and returns
     // the row of generation g+t+1 that sits one row above x.
@@ -504,8 +506,8 @@ __device__ __forceinline__ void march(const MarchArgs &A, uint32_t &flag_alive, 
         constexpr bool WARM = decltype(warm_tag)::value;
         uint32_t x0[kWL], fin[kWL];
 #pragma unroll
-        for (int j = 0; j < kWL; ++j) { x0[j] = q0[j]; q0[j] = q1[j]; fin[j] = 0; }
-        if (r + 2 < rload_end) load_row(q1);
+        for (int j = 0; j < kWL; ++j) { x0[j] = q[decltype(par_tag)::value][j]; fin[j] = 0; }
+        if (r + 2 < rload_end) load_row(q[decltype(par_tag)::value]);
         const bool emit = !WARM && r - LAG >= A.y0;
 #if GOL_SKEW
         // descending: level t+1 has already consumed pend[t+1] when level t overwrites it
