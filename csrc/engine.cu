@@ -90,6 +90,7 @@ struct gol_engine {
     bool use_persistent = false;    // GOL_PERSISTENT=1: one dataflow launch per batch instead of one per epoch
     int persist_ctas[9] = {0};
     int tuned_rows[17] = {0};       // measured best chunk height per temporal depth (0 = not tuned yet)
+    int pipe_lv = 0, pipe_d = 0;    // GOL_PIPE=LVxD: warp-pipelined kernel for epochs of LV*D generations
     bool autotune = true;           // GOL_AUTOTUNE=0 disables the one-off geometry timing      // max co-resident CTAs of the persistent kernel per k (0 = not queried)
 
     // dense path (tiny grids, single domain)
@@ -225,6 +226,9 @@ int upload_domains(gol_engine *e)
 
 // Launch geometry for temporal depth k: chunk height trades apron redundancy (2k rows per
 // chunk) against the number of independent warps.
+bool uses_pipe(const gol_engine *e, int k);
+int items_per_cta(const gol_engine *e, int k);
+
 void geometry(const gol_engine *e, int k, GolLaunch *lp, int resident_warps_per_sm = 0)
 {
     static const int env_warps = getenv("GOL_WARPS_PER_SM") ? atoi(getenv("GOL_WARPS_PER_SM")) : 0;
@@ -232,7 +236,7 @@ void geometry(const gol_engine *e, int k, GolLaunch *lp, int resident_warps_per_
         const int64_t rows = e->tuned_rows[k], chunks = gol_div_up(e->max_h, rows);
         lp->chunk_rows = (int32_t)rows;
         lp->chunks = (int32_t)chunks;
-        lp->ctas_per_domain = (int32_t)gol_div_up(chunks * e->max_strips, 4);
+        lp->ctas_per_domain = (int32_t)gol_div_up(chunks * e->max_strips, items_per_cta(e, k));
         return;
     }
     const int warps_per_sm = env_warps ? env_warps : (resident_warps_per_sm ? resident_warps_per_sm : 16);
@@ -247,14 +251,26 @@ void geometry(const gol_engine *e, int k, GolLaunch *lp, int resident_warps_per_
     chunks = gol_div_up(e->max_h, rows);
     lp->chunk_rows = (int32_t)rows;
     lp->chunks = (int32_t)chunks;
-    lp->ctas_per_domain = (int32_t)gol_div_up(chunks * e->max_strips, 4);
+    lp->ctas_per_domain = (int32_t)gol_div_up(chunks * e->max_strips, items_per_cta(e, k));
 }
 
 bool multi(const gol_engine *e) { return e->P > 1; }
 
-// largest temporal depth the strip kernel is instantiated for that does not exceed cap
-int pick_depth(int64_t cap)
+bool uses_pipe(const gol_engine *e, int k) { return e->pipe_d > 0 && k == e->pipe_lv * e->pipe_d; }
+
+// work items per CTA for depth k (the strip kernel packs 4 items into a CTA, the pipeline kernel 1)
+int items_per_cta(const gol_engine *e, int k) { return uses_pipe(e, k) ? 1 : 4; }
+
+int launch_generation_kernel(gol_engine *e, const GolLaunch &lp, int k, int flags)
 {
+    if (uses_pipe(e, k)) return gol_launch_pipe(e->d_doms, e->per_proc, lp, e->pipe_lv, e->pipe_d, flags, e->stream);
+    return gol_launch_strip(e->d_doms, e->per_proc, lp, k, flags, e->stream);
+}
+
+// largest temporal depth the strip kernel is instantiated for that does not exceed cap
+int pick_depth(int64_t cap, const gol_engine *e = nullptr)
+{
+    if (e && e->pipe_d > 0 && e->kmax == e->pipe_lv * e->pipe_d && cap >= e->kmax) return e->kmax;
     if (cap >= 16) return 16;
     if (cap >= 8) return 8;
     return (int)std::max<int64_t>(1, cap);
@@ -282,7 +298,7 @@ int launch_epoch(gol_engine *e, int k, int in, int out, bool flags, int rec_slot
     if (dbg & 4) lp.wait_seq = 0;
     lp.rec_slot = flags ? rec_slot : -1;
     lp.rec_seq = rec_seq;
-    GOL_TRY(gol_launch_strip(e->d_doms, e->per_proc, lp, k, flags ? 1 : 0, e->stream));
+    GOL_TRY(launch_generation_kernel(e, lp, k, flags ? 1 : 0));
     ++e->launches;
     return 0;
 }
@@ -303,8 +319,9 @@ int autotune_geometry(gol_engine *e, int k, int in, int scratch)
     }
     // heights that fill the machine exactly: m full waves of resident CTAs, no partial last wave
     int occ = 0;
-    if (gol_strip_ctas_per_sm(k, &occ) == 0 && occ > 0) {
-        const int64_t slots = (int64_t)e->num_sms * occ * 4 / std::max(1, e->per_proc);  // warps = work items
+    const bool pipe = uses_pipe(e, k);
+    if ((pipe ? gol_pipe_ctas_per_sm(e->pipe_lv, e->pipe_d, &occ) : gol_strip_ctas_per_sm(k, &occ)) == 0 && occ > 0) {
+        const int64_t slots = (int64_t)e->num_sms * occ * items_per_cta(e, k) / std::max(1, e->per_proc);  // resident work items
         for (int m = 1; m <= 3; ++m) {
             const int64_t chunks = m * slots / e->max_strips;
             if (chunks < 1) continue;
@@ -321,16 +338,16 @@ int autotune_geometry(gol_engine *e, int k, int in, int scratch)
         GolLaunch lp{};
         lp.chunk_rows = rows;
         lp.chunks = (int32_t)gol_div_up(e->max_h, rows);
-        lp.ctas_per_domain = (int32_t)gol_div_up((int64_t)lp.chunks * e->max_strips, 4);
+        lp.ctas_per_domain = (int32_t)gol_div_up((int64_t)lp.chunks * e->max_strips, items_per_cta(e, k));
         lp.in_idx = in;
         lp.out_idx = scratch;
         lp.seq = e->seq;
         lp.wait_seq = 0;
         lp.signal = 3 << 8;  // no pushes, no flags
         lp.rec_slot = -1;
-        GOL_TRY(gol_launch_strip(e->d_doms, e->per_proc, lp, k, 0, e->stream));
+        GOL_TRY(launch_generation_kernel(e, lp, k, 0));
         GOL_CUDA(cudaEventRecord(e->ev_tune[0], e->stream));
-        for (int i = 0; i < 3; ++i) GOL_TRY(gol_launch_strip(e->d_doms, e->per_proc, lp, k, 0, e->stream));
+        for (int i = 0; i < 3; ++i) GOL_TRY(launch_generation_kernel(e, lp, k, 0));
         GOL_CUDA(cudaEventRecord(e->ev_tune[1], e->stream));
         GOL_CUDA(cudaEventSynchronize(e->ev_tune[1]));
         e->launches += 4;
@@ -371,7 +388,7 @@ int run_epochs(gol_engine *e, int64_t n, int keep, bool want_flags, bool per_gen
     // Leading run of full-depth epochs: one persistent (dataflow) launch instead of one launch
     // per epoch.  The flagged last epoch of a batch and remainder epochs stay classic launches.
     if (!per_gen_flags && e->use_persistent) {
-        const int kp = pick_depth(std::min<int64_t>(left, kcap));
+        const int kp = pick_depth(std::min<int64_t>(left, kcap), e);
         int64_t count = left / kp;
         if (want_flags && count * kp == left) --count;
         int rot[3], nrot = 0;
@@ -409,7 +426,7 @@ int run_epochs(gol_engine *e, int64_t n, int keep, bool want_flags, bool per_gen
     while (left > 0) {
         int k = 1;
         if (!per_gen_flags) {
-            k = pick_depth(std::min<int64_t>(left, kcap));
+            k = pick_depth(std::min<int64_t>(left, kcap), e);
         }
         int out = -1;
         for (int i = 0; i < GOL_NBUF; ++i)
@@ -814,6 +831,14 @@ static int engine_create_impl(gol_engine *e)
     e->items_cap = (int64_t)e->max_strips * gol_div_up(e->max_h, 8) + 64;
     if (const char *v = getenv("GOL_PERSISTENT")) e->use_persistent = atoi(v) != 0;
     if (const char *v = getenv("GOL_AUTOTUNE")) e->autotune = atoi(v) != 0;
+    if (const char *v = getenv("GOL_PIPE")) {
+        int lv = 0, d = 0, occ = 0;
+        if (sscanf(v, "%dx%d", &lv, &d) == 2 && lv * d <= GOL_GHOST_ROWS && gol_pipe_ctas_per_sm(lv, d, &occ) == 0) {
+            e->pipe_lv = lv;
+            e->pipe_d = d;
+            if (e->cfg.k_max <= 0) e->kmax = lv * d;
+        }
+    }
     if (getenv("GOL_VERBOSE")) e->cfg.flags |= GOL_FLAG_VERBOSE;
     GOL_TRY(build_arena_layout(e, e->rank, &e->arena_layout));
     GOL_CUDA(cudaMalloc(&e->arena, (size_t)e->arena_layout.total));

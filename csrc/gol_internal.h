@@ -131,6 +131,9 @@ int gol_launch_halo(const GolDomainDev *d_doms, int ndoms, const GolLaunch &lp, 
 int gol_strip_geometry(int nw32, int *strips);
 int gol_persistent_max_ctas(int k, int device, int *ctas);
 int gol_strip_ctas_per_sm(int k, int *ctas_per_sm);
+int gol_launch_pipe(const GolDomainDev *d_doms, int ndoms, const GolLaunch &lp, int lv, int d, int want_flags,
+                    CUstream_st *stream);
+int gol_pipe_ctas_per_sm(int lv, int d, int *ctas_per_sm);
 int gol_launch_persistent(const GolDomainDev *d_doms, const GolPersist &pp, int k, int ctas, CUstream_st *stream);
 int gol_launch_scan_alive(const GolDomainDev *d_doms, int ndoms, const GolLaunch &lp, CUstream_st *stream);
 int gol_write_all(int fd, const char *buf, size_t len, int64_t offset, const char *path);

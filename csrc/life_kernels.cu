@@ -376,6 +376,14 @@ __device__ __forceinline__ uint32_t mad_lo(uint32_t a, uint32_t b, uint32_t c)
     return d;
 }
 
+// Shared-memory row FIFO between two consecutive pipeline stages (warps) of a CTA: kRingRows rows of
+// 64 words; `head` counts rows produced, `tail` rows consumed.
+constexpr int kRingRows = 8;
+struct RingPort {
+    uint32_t *data;
+    volatile int *head, *tail;
+};
+
 struct MarchArgs {
     const uint32_t *in;   // padded input buffer (global)
     uint32_t *out;        // padded output buffer (global)
@@ -385,6 +393,8 @@ struct MarchArgs {
     uint32_t keep[kWL];   // per-word ownership / tail mask of this lane
     int mode;             // 1 plain vector load, 2 composed ragged tail, 0 nothing to load
     uint32_t two, four;   // run-time 2 and 4 (see GOL_ONE_SIDED)
+    RingPort rin, rout;   // pipeline kernel only: row source / sink in shared memory
+    int lane;
 };
 
 // One warp streams rows [y0-K, y1+K) of generation g through K register-resident levels and
@@ -403,7 +413,7 @@ struct MarchArgs {
 #define GOL_WARM_SPLIT 1   // prune the inactive levels of the pipeline fill (see march)
 #endif
 
-template <int K, bool FLAGS, bool FAST>
+template <int K, bool FLAGS, bool FAST, bool SRC_RING = false, bool DST_RING = false>
 __device__ __forceinline__ void march(const MarchArgs &A, uint32_t &flag_alive, uint32_t &flag_diff)
 {
     constexpr int LAG = GOL_SKEW ? 2 * K - 1 : K;  // a step that consumes level-0 row r emits row r - LAG
@@ -415,7 +425,21 @@ __device__ __forceinline__ void march(const MarchArgs &A, uint32_t &flag_alive, 
     const uint32_t *pin = A.in + (int64_t)(rbeg + G) * pitch + GOL_GHOST_WORDS32;  // row being loaded
     uint32_t *pout = A.out + (int64_t)(A.y0 + G) * pitch + GOL_GHOST_WORDS32 + A.vi;
 
+    int n_in = 0, seen_head = 0, n_out = 0, seen_tail = 0;  // ring bookkeeping (pipeline stages)
     auto load_row = [&](uint32_t(&w)[kWL]) {
+        if (SRC_RING) {
+            // rows before n_in have been copied out of the ring: hand their slots back
+            // (the row fetched by the previous call may still be in flight; everything before it has
+            // been moved on into the level-0 registers)
+            __syncwarp();
+            if (A.lane == 0 && n_in > 0) *A.rin.tail = n_in - 1;
+            while (seen_head <= n_in) seen_head = *A.rin.head;
+            __threadfence_block();
+            const uint2 v = *reinterpret_cast<const uint2 *>(A.rin.data + (n_in % kRingRows) * 64 + A.lane * kWL);
+            w[0] = v.x; w[1] = v.y;
+            ++n_in;
+            return;
+        }
         if (FAST || A.mode == 1) {
             const uint2 v = ldg_v2(pin + A.vi);
             w[0] = v.x; w[1] = v.y;
@@ -546,7 +570,14 @@ __device__ __forceinline__ void march(const MarchArgs &A, uint32_t &flag_alive, 
                 for (int j = 0; j < kWL; ++j) fin[j] = __funnelshift_r(fin[j], j < kWL - 1 ? fin[j + 1] : up, K);
             }
 #endif
-            if (emit) {  // fin = row (r - LAG) of generation g+K
+            if (emit && DST_RING) {  // hand the row (all 64 words, aprons included) to the next stage
+                while (n_out - seen_tail >= kRingRows) seen_tail = *A.rout.tail;
+                *reinterpret_cast<uint2 *>(A.rout.data + (n_out % kRingRows) * 64 + A.lane * kWL) = make_uint2(fin[0], fin[1]);
+                ++n_out;
+                __threadfence_block();
+                __syncwarp();
+                if (A.lane == 0) *A.rout.head = n_out;
+            } else if (emit) {  // fin = row (r - LAG) of generation g+K
                 if (FAST) {
                     if (store_all) stg_v2(pout, fin[0], fin[1]);
                 } else if (store_any) {
@@ -618,6 +649,7 @@ __device__ __forceinline__ void run_item(const GolDomainDev &D, const ItemCtx &c
     A.out = reinterpret_cast<uint32_t *>(__cvta_generic_to_global(D.buf[c.out_idx]));
     A.vi = strip_origin(strip, S, A.nw) - kWL + lane * kWL;
     A.y0 = y0; A.y1 = y1;
+    A.lane = lane;
     A.two = D.mul2; A.four = D.mul4;
     if (c.wait_seq && border) wait_neighbors(D, c.wait_seq, lane, c.skip_mask);
 
@@ -681,6 +713,89 @@ __global__ void __launch_bounds__(kWarps * 32, K == 8 ? GOL_K8_MINBLOCKS : (K ==
         run_item<K, FLAGS>(D, c, im, strip, chunk, border, lane);
     }
     if (lp.rec_slot >= 0) finish_domain(D, lp);
+}
+
+// ---------------------------------------------------------- pipeline kernel
+// One CTA per work item, D warps per CTA: warp s runs generations s*LV .. (s+1)*LV-1 of the item
+// and hands each finished row to warp s+1 through a shared-memory row FIFO, so an item advances
+// K = LV*D generations per pass while every warp only keeps LV levels in registers.  Compared
+// with one warp doing all K levels this (a) lets K grow without the register file limiting
+// occupancy and (b) makes a chunk D times taller for the same number of resident warps, which
+// divides the relative cost of the pipeline fill ((K+1) rows per chunk) by D.
+template <int LV, int D, bool FLAGS>
+__global__ void __launch_bounds__(32 * D) life_pipe_kernel(const GolDomainDev *__restrict__ doms, const GolLaunch lp)
+{
+    __shared__ __align__(16) uint32_t ring[D > 1 ? D - 1 : 1][kRingRows * 64];
+    __shared__ int heads[D], tails[D];
+    if (threadIdx.x < D) { heads[threadIdx.x] = 0; tails[threadIdx.x] = 0; }
+    __syncthreads();
+    const int dom_id = blockIdx.x / lp.ctas_per_domain;
+    const int item = blockIdx.x - dom_id * lp.ctas_per_domain;
+    const GolDomainDev &Dm = doms[dom_id];
+    const int lane = threadIdx.x & 31, stage = threadIdx.x >> 5;
+    const ItemMap im = item_map(Dm, lp.chunk_rows);
+    int strip = 0, chunk = 0;
+    bool border = false;
+    if (decode_item(im, item, strip, chunk, border)) {
+        const int S = im.S, H = Dm.H;
+        const int y0 = chunk * lp.chunk_rows, y1 = min(H, y0 + lp.chunk_rows);
+        MarchArgs A;
+        A.nw = Dm.nw32; A.nwf = Dm.nwf32; A.rem = Dm.rem; A.pitch = Dm.pitch32;
+        A.in = reinterpret_cast<const uint32_t *>(__cvta_generic_to_global(Dm.buf[lp.in_idx]));
+        A.out = reinterpret_cast<uint32_t *>(__cvta_generic_to_global(Dm.buf[lp.out_idx]));
+        A.vi = strip_origin(strip, S, A.nw) - kWL + lane * kWL;
+        A.lane = lane;
+        A.two = Dm.mul2; A.four = Dm.mul4;
+        // stage s produces generation (s+1)*LV for the rows the later stages still need
+        A.y0 = y0 - (D - 1 - stage) * LV;
+        A.y1 = y1 + (D - 1 - stage) * LV;
+        if (stage > 0) { A.rin.data = ring[stage - 1]; A.rin.head = &heads[stage - 1]; A.rin.tail = &tails[stage - 1]; }
+        if (stage < D - 1) { A.rout.data = ring[stage]; A.rout.head = &heads[stage]; A.rout.tail = &tails[stage]; }
+        if (stage == 0 && lp.wait_seq && border) wait_neighbors(Dm, lp.wait_seq, lane);
+
+        const bool owned_lane = lane >= 1 && lane <= kValidLanes;
+#pragma unroll
+        for (int j = 0; j < kWL; ++j) {
+            const int i = A.vi + j;
+            uint32_t kmask = (owned_lane && i >= 0 && i < A.nw) ? 0xffffffffu : 0u;
+            if (A.rem) {
+                if (i == A.nwf) kmask &= A.rem >= 32 ? 0xffffffffu : ((1u << A.rem) - 1u);
+                if (i == A.nwf + 1) kmask &= A.rem > 32 ? ((1u << (A.rem - 32)) - 1u) : 0u;
+            }
+            A.keep[j] = kmask;
+        }
+        if (A.rem == 0) A.mode = (A.vi >= -GOL_GHOST_WORDS32 && A.vi + kWL <= A.nw + GOL_GHOST_WORDS32) ? 1 : 0;
+        else A.mode = (A.vi >= -GOL_GHOST_WORDS32 && A.vi + kWL <= A.nwf) ? 1 : (A.vi < A.nwf + 4 && A.vi + kWL > A.nwf ? 2 : 0);
+        const bool all_or_none = (A.keep[0] & A.keep[1]) == 0xffffffffu || (A.keep[0] | A.keep[1]) == 0u;
+        const bool fast = __all_sync(0xffffffffu, A.mode == 1 && all_or_none);
+
+        uint32_t fa = 0, fd = 0;
+        if (D == 1) {
+            if (fast) march<LV, FLAGS, true>(A, fa, fd); else march<LV, FLAGS, false>(A, fa, fd);
+        } else if (stage == 0) {
+            if (fast) march<LV, false, true, false, true>(A, fa, fd); else march<LV, false, false, false, true>(A, fa, fd);
+        } else if (stage == D - 1) {
+            if (fast) march<LV, FLAGS, true, true, false>(A, fa, fd); else march<LV, FLAGS, false, true, false>(A, fa, fd);
+        } else {
+            march<LV, false, true, true, true>(A, fa, fd);  // ring to ring: no global access, no special lanes
+        }
+        if (stage == D - 1) {
+            if (FLAGS) {
+                const bool a = __any_sync(0xffffffffu, fa != 0);
+                const bool d = __any_sync(0xffffffffu, fd != 0);
+                if (lane == 0) {
+                    if (a) atomicOr(&Dm.scratch->alive, 1u);
+                    if (d) atomicOr(&Dm.scratch->diff, 1u);
+                }
+            }
+            __syncwarp();
+            if (border) {
+                push_borders(Dm, lp.out_idx, strip, y0, y1, lane, lp.signal >> 8);
+                if (lp.signal & 1) border_item_done(Dm, lp, im.nborder, lane);
+            }
+        }
+    }
+    if (lp.rec_slot >= 0) finish_domain(Dm, lp);
 }
 
 // ------------------------------------------------------- persistent kernel
@@ -1013,6 +1128,43 @@ int gol_launch_persistent(const GolDomainDev *d_doms, const GolPersist &pp, int 
     // item-to-item waits rely on
     cudaError_t err = cudaLaunchCooperativeKernel(fn, dim3((unsigned)ctas), dim3(kWarps * 32), args, 0, stream);
     if (err != cudaSuccess) GOL_FAIL("life_persistent_kernel<k=%d> launch failed: %s", k, cudaGetErrorString(err));
+    return 0;
+}
+
+template <int LV, int D>
+static cudaError_t launch_pipe_t(const GolDomainDev *d, int grid, const GolLaunch &lp, int want_flags, cudaStream_t s)
+{
+    if (want_flags) life_pipe_kernel<LV, D, true><<<grid, 32 * D, 0, s>>>(d, lp);
+    else life_pipe_kernel<LV, D, false><<<grid, 32 * D, 0, s>>>(d, lp);
+    return cudaGetLastError();
+}
+template <int LV, int D>
+static cudaError_t pipe_occupancy(int *ctas_per_sm)
+{
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(ctas_per_sm, life_pipe_kernel<LV, D, false>, 32 * D, 0);
+}
+
+#define GOL_PIPE_CONFIGS(X) X(4, 2) X(2, 4) X(4, 4) X(2, 8) X(8, 2) X(3, 4) X(4, 3) X(5, 2) X(6, 2) X(3, 3)
+
+int gol_launch_pipe(const GolDomainDev *d_doms, int ndoms, const GolLaunch &lp, int lv, int d, int want_flags,
+                    CUstream_st *stream)
+{
+    const int grid = ndoms * lp.ctas_per_domain;
+    cudaError_t err = cudaErrorInvalidValue;
+#define GOL_X(LV, DD) if (lv == LV && d == DD) err = launch_pipe_t<LV, DD>(d_doms, grid, lp, want_flags, stream);
+    GOL_PIPE_CONFIGS(GOL_X)
+#undef GOL_X
+    if (err != cudaSuccess) GOL_FAIL("life_pipe_kernel<%d,%d> launch failed: %s", lv, d, cudaGetErrorString(err));
+    return 0;
+}
+
+int gol_pipe_ctas_per_sm(int lv, int d, int *ctas_per_sm)
+{
+    cudaError_t err = cudaErrorInvalidValue;
+#define GOL_X(LV, DD) if (lv == LV && d == DD) err = pipe_occupancy<LV, DD>(ctas_per_sm);
+    GOL_PIPE_CONFIGS(GOL_X)
+#undef GOL_X
+    if (err != cudaSuccess) GOL_FAIL("pipeline kernel <%d,%d>: %s", lv, d, cudaGetErrorString(err));
     return 0;
 }
 

@@ -262,3 +262,15 @@ def test_cli_one_process_per_gpu(cuda_device, tmp_path):
     assert (tmp_path / "collective_output.out").read_bytes() == (tmp_path / "cuda_output.out").read_bytes()
     want = cpu.format_text(cpu.step(cpu.random_grid(n, n, 44), n, 100), n)
     assert (tmp_path / "cuda_output.out").read_bytes() == want
+
+
+@pytest.mark.parametrize("cfg", ["4x2", "2x4", "4x4"])
+def test_warp_pipelined_kernel(cuda_device, cfg):
+    # opt-in kernel variant (GOL_PIPE=LVxD): D warps of a CTA form a pipeline of LV generations each,
+    # rows travel through shared-memory FIFOs; must be bit-identical to the oracle like the default
+    import sys
+    env = dict(os.environ, GOL_PIPE=cfg)
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "pipe_check.py"), "--no-timing"],
+                       capture_output=True, text=True, timeout=300, env=env)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    assert "pipe check ok" in p.stdout
