@@ -83,7 +83,11 @@ struct gol_engine {
     unsigned long long *d_results = nullptr;  // [kMaxBatch + 1]
     unsigned long long *h_results = nullptr;  // pinned
     unsigned int *d_error = nullptr;
-    uint64_t *stage = nullptr;      // dense staging buffer for linear host<->device copies (largest local domain)
+    uint64_t *stage = nullptr;      // dense staging buffer for linear host->device copies (all local domains)
+    std::vector<size_t> stage_off;  // word offset of each local domain inside `stage`
+    cudaStream_t copy_stream = nullptr;  // staged (overlapped) uploads run here
+    cudaEvent_t ev_staged = nullptr, ev_stage_free = nullptr;
+    bool staged = false, stage_busy = false;
     int max_strips = 1;
     int64_t max_h = 1;
     int64_t items_cap = 0;          // per-domain capacity of the item flag array
@@ -757,6 +761,9 @@ void gol_engine_destroy(gol_engine *e)
     if (e->h_results) cudaFreeHost(e->h_results);
     if (e->d_error) cudaFree(e->d_error);
     if (e->stage) cudaFree(e->stage);
+    if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
+    if (e->ev_staged) cudaEventDestroy(e->ev_staged);
+    if (e->ev_stage_free) cudaEventDestroy(e->ev_stage_free);
     for (auto &d : e->dense)
         if (d) cudaFree(d);
     if (e->d_dflags) cudaFree(e->d_dflags);
@@ -854,8 +861,14 @@ static int engine_create_impl(gol_engine *e)
     GOL_CUDA(cudaMemset(e->d_error, 0, 2 * sizeof(unsigned int)));
     {
         size_t stage_bytes = 0;
-        for (const LocalDomain &ld : e->local) stage_bytes = std::max(stage_bytes, (size_t)ld.L.nq * (size_t)ld.L.height * 8);
+        for (const LocalDomain &ld : e->local) {
+            e->stage_off.push_back(stage_bytes / 8);
+            stage_bytes += (size_t)ld.L.nq * (size_t)ld.L.height * 8;
+        }
         GOL_CUDA(cudaMalloc(&e->stage, stage_bytes));
+        GOL_CUDA(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
+        GOL_CUDA(cudaEventCreateWithFlags(&e->ev_staged, cudaEventDisableTiming));
+        GOL_CUDA(cudaEventCreateWithFlags(&e->ev_stage_free, cudaEventDisableTiming));
     }
     if (e->P == 1) {
         GOL_TRY(upload_domains(e));
@@ -1021,9 +1034,10 @@ int gol_engine_load_packed(gol_engine *e, const uint64_t *host)
             // full-width domain: its rows are contiguous in the host grid - one linear DMA into the
             // staging buffer (a strided 2-D copy of 2 KiB rows runs far below PCIe speed), then a
             // kernel spreads the rows into the padded layout
-            GOL_CUDA(cudaMemcpyAsync(e->stage, host + ld.y0 * nqg, (size_t)ld.L.nq * (size_t)ld.L.height * 8,
-                                     cudaMemcpyHostToDevice, e->stream));
-            GOL_TRY(gol_launch_dense_to_padded(e->stage, ld.L.nq, 0, reinterpret_cast<uint32_t *>(dst), ld.L, e->stream));
+            GOL_CUDA(cudaMemcpyAsync(e->stage + e->stage_off[(size_t)i], host + ld.y0 * nqg,
+                                     (size_t)ld.L.nq * (size_t)ld.L.height * 8, cudaMemcpyHostToDevice, e->stream));
+            GOL_TRY(gol_launch_dense_to_padded(e->stage + e->stage_off[(size_t)i], ld.L.nq, 0,
+                                               reinterpret_cast<uint32_t *>(dst), ld.L, e->stream));
             ++e->launches;
         } else {
             GOL_CUDA(cudaMemcpy2DAsync(dst + ((int64_t)G * ld.L.pitch32 + GOL_GHOST_WORDS32) * 4, (size_t)ld.L.pitch32 * 4,
@@ -1032,6 +1046,52 @@ int gol_engine_load_packed(gol_engine *e, const uint64_t *host)
         }
     }
     GOL_CUDA(cudaStreamSynchronize(e->stream));
+    return 0;
+}
+
+// Overlapped upload for a stream of grids: stage() starts the host->device copy of the NEXT grid
+// on a second stream into the staging buffer and returns at once (the host memory must be pinned
+// for the copy to be asynchronous and must stay untouched until commit); commit() makes the staged
+// grid the current one (a kernel spreads it into the padded layout).  While the engine runs grid i,
+// grid i+1 is already crossing PCIe.
+int gol_engine_stage_packed(gol_engine *e, const uint64_t *host)
+{
+    GOL_CUDA(cudaSetDevice(e->cfg.device));
+    if (!e->fast) GOL_FAIL("gol_engine_stage_packed: only for engines on the strip path (use gol_engine_load_packed)");
+    const int64_t nqg = gol_div_up(e->cfg.width, 64);
+    if (e->stage_busy) GOL_CUDA(cudaStreamWaitEvent(e->copy_stream, e->ev_stage_free, 0));  // last commit still reads it
+    for (int i = 0; i < e->per_proc; ++i) {
+        const LocalDomain &ld = e->local[(size_t)i];
+        uint64_t *dst = e->stage + e->stage_off[(size_t)i];
+        if (ld.L.nq == nqg)
+            GOL_CUDA(cudaMemcpyAsync(dst, host + ld.y0 * nqg, (size_t)ld.L.nq * (size_t)ld.L.height * 8,
+                                     cudaMemcpyHostToDevice, e->copy_stream));
+        else
+            GOL_CUDA(cudaMemcpy2DAsync(dst, (size_t)ld.L.nq * 8, host + ld.y0 * nqg + ld.x0 / 64, (size_t)nqg * 8,
+                                       (size_t)ld.L.nq * 8, (size_t)ld.L.height, cudaMemcpyHostToDevice, e->copy_stream));
+    }
+    GOL_CUDA(cudaEventRecord(e->ev_staged, e->copy_stream));
+    e->staged = true;
+    return 0;
+}
+
+int gol_engine_commit_staged(gol_engine *e)
+{
+    GOL_CUDA(cudaSetDevice(e->cfg.device));
+    if (!e->staged) GOL_FAIL("gol_engine_commit_staged: nothing staged");
+    GOL_TRY(clear_current(e));
+    GOL_CUDA(cudaStreamWaitEvent(e->stream, e->ev_staged, 0));
+    for (int i = 0; i < e->per_proc; ++i) {
+        const LocalDomain &ld = e->local[(size_t)i];
+        char *dst = e->arena + e->arena_layout.buf_off[(size_t)i * GOL_NBUF + e->cur];
+        GOL_CUDA(cudaMemsetAsync(dst, 0, (size_t)ld.L.buffer_words32 * 4, e->stream));
+        GOL_TRY(gol_launch_dense_to_padded(e->stage + e->stage_off[(size_t)i], ld.L.nq, 0, reinterpret_cast<uint32_t *>(dst),
+                                           ld.L, e->stream));
+        ++e->launches;
+    }
+    GOL_CUDA(cudaEventRecord(e->ev_stage_free, e->stream));
+    e->stage_busy = true;
+    e->staged = false;
     return 0;
 }
 

@@ -100,6 +100,8 @@ def _proto(lib):
         "gol_engine_ipc_import": (i32, [vp, vp]),
         "gol_engine_load_packed": (i32, [vp, vp]),
         "gol_engine_load_packed_device": (i32, [vp, vp, i64, i64, i64, i64]),
+        "gol_engine_stage_packed": (i32, [vp, vp]),
+        "gol_engine_commit_staged": (i32, [vp]),
         "gol_engine_randomize": (i32, [vp, u64]),
         "gol_engine_load_text_file": (i32, [vp, C.c_char_p, i32]),
         "gol_engine_store_text_file": (i32, [vp, C.c_char_p]),

@@ -186,6 +186,28 @@ class GameOfLife:
         self._after_load()
         return self
 
+    def stage_packed(self, packed) -> "GameOfLife":
+        """Start uploading the NEXT grid (pinned torch int64 CPU tensor or numpy uint64, global packed
+        shape) on a second stream and return immediately; the engine may still be running the current
+        grid.  Keep `packed` alive and unchanged until commit_staged()."""
+        torch = self._torch
+        if isinstance(packed, torch.Tensor):
+            keep, ptr = packed, packed.contiguous().data_ptr()
+        else:
+            keep = np.ascontiguousarray(packed, dtype=np.uint64)
+            ptr = keep.ctypes.data
+        if tuple(keep.shape) != (self.config.height, words_per_row(self.config.width)):
+            raise ValueError("packed grid has the wrong shape")
+        self._staged_keepalive = keep
+        N.check(self._lib.gol_engine_stage_packed(self._h, C.c_void_p(ptr)), "stage_packed")
+        return self
+
+    def commit_staged(self) -> "GameOfLife":
+        """Make the staged grid the current one (then run()/step() as after load_packed)."""
+        N.check(self._lib.gol_engine_commit_staged(self._h), "commit_staged")
+        self._after_load()
+        return self
+
     def load(self, cells) -> "GameOfLife":
         """uint8/bool [H, W] cells (numpy, or a torch tensor on CPU or GPU)."""
         torch = self._torch

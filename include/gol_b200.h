@@ -201,6 +201,11 @@ int gol_engine_ipc_import(gol_engine *e, const void *all_blobs);
 
 /* Grid load/store.  Every process passes the same arguments. */
 int gol_engine_load_packed(gol_engine *e, const uint64_t *host_packed); /* global dense    */
+/* Overlapped upload for a stream of grids: stage() starts the (asynchronous, if `host_packed` is
+ * pinned) copy of the next global grid on a second stream and returns; commit() turns the staged
+ * grid into the current one.  Between the two calls the engine may be running the previous grid. */
+int gol_engine_stage_packed(gol_engine *e, const uint64_t *host_packed);
+int gol_engine_commit_staged(gol_engine *e);
 int gol_engine_load_packed_device(gol_engine *e, const uint64_t *d_packed, int64_t x0,
                                   int64_t y0, int64_t w, int64_t h);    /* one local block */
 int gol_engine_randomize(gol_engine *e, uint64_t seed);

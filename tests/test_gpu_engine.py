@@ -274,3 +274,21 @@ def test_warp_pipelined_kernel(cuda_device, cfg):
                        capture_output=True, text=True, timeout=300, env=env)
     assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
     assert "pipe check ok" in p.stdout
+
+
+def test_staged_upload(cuda_device):
+    from gol_b200.ops import cpu
+    w, h = 1100, 200
+    a, b = cpu.random_grid(w, h, 1), cpu.random_grid(w, h, 2)
+    for grid in [(1, 1), (2, 2)]:
+        life = make(w, h, grid=grid, gen_limit=20)
+        ta = torch.from_numpy(a.view(np.int64)).pin_memory()
+        tb = torch.from_numpy(b.view(np.int64)).pin_memory()
+        life.stage_packed(ta).commit_staged()
+        life.stage_packed(tb)                      # uploads while the first grid runs
+        r1 = life.run()
+        assert np.array_equal(life.packed_numpy(), cpu.run(a, w, gen_limit=20)[0]) and r1.generations == 20
+        life.commit_staged()
+        life.run()
+        assert np.array_equal(life.packed_numpy(), cpu.run(b, w, gen_limit=20)[0])
+        life.close()
