@@ -434,7 +434,7 @@ int run_epochs(gol_engine *e, int64_t n, int keep, bool want_flags, bool per_gen
         }
         int out = -1;
         for (int i = 0; i < GOL_NBUF; ++i)
-            if (i != in && i != e->prev_in && i != keep && i != keep2) { out = i; break; }
+            if (i != in && (i != e->prev_in || !multi(e)) && i != keep && i != keep2) { out = i; break; }
         if (out < 0)  // prev_in is only a hazard between ranks that run ahead; never when it is the last choice
             for (int i = 0; i < GOL_NBUF; ++i)
                 if (i != in && i != keep && i != keep2) { out = i; break; }
