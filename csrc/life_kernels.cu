@@ -51,9 +51,17 @@ __device__ __forceinline__ uint32_t maj3(uint32_t a, uint32_t b, uint32_t c) { r
 // Next state of 32 cells from the bit-sliced 3-cell row sums (s0 + 2*s1, centre included) of
 // the rows above (a), at (b) and below (n) and the centre word m.  T = 9-cell sum:
 // alive' = (T == 3) | (m & T == 4).
+// Seven LOP3: the column of low bits is encoded as (parity, all-equal) instead of (parity, carry);
+// with that encoding the remaining 5-input function has a 3-gate realisation (found by the
+// exhaustive search in scripts/search/lop3_search.c; none exists for the (parity, carry) encoding,
+// and no 2-gate one for any encoding).  GOL_RULE8 keeps the former 8-gate form for comparison.
+#ifndef GOL_RULE8
+#define GOL_RULE8 0
+#endif
 __device__ __forceinline__ uint32_t life_rule(uint32_t a0, uint32_t a1, uint32_t b0, uint32_t b1,
                                               uint32_t n0, uint32_t n1, uint32_t m)
 {
+#if GOL_RULE8
     const uint32_t x0 = xor3(a0, b0, n0);
     const uint32_t k0 = maj3(a0, b0, n0);
     const uint32_t x1 = xor3(a1, b1, n1);
@@ -62,6 +70,15 @@ __device__ __forceinline__ uint32_t life_rule(uint32_t a0, uint32_t a1, uint32_t
     const uint32_t h = lop3<0x42>(k0, x1, k1);   // ~(k0 ^ x1) & (k1 ^ (k0&x1)) : T in {4,5}
     const uint32_t u = lop3<0x08>(x0, h, m);     // ~x0 & h & m                 : T == 4, alive
     return lop3<0xEA>(x0, g, u);                 // (x0 & g) | u
+#else
+    const uint32_t p0 = xor3(a0, b0, n0);        // low column: count odd
+    const uint32_t e0 = lop3<0x81>(a0, b0, n0);  // low column: count 0 or 3
+    const uint32_t p1 = xor3(a1, b1, n1);        // high column: count odd
+    const uint32_t k1 = maj3(a1, b1, n1);        // high column: count >= 2
+    const uint32_t g1 = lop3<0x56>(p0, e0, k1);
+    const uint32_t g2 = lop3<0xA4>(p0, m, g1);
+    return lop3<0x60>(g2, e0, p1);
+#endif
 }
 
 // Experiment kept for the record (off): funnel shifts by one bit on the FMA pipe instead of the
