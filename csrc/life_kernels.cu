@@ -58,6 +58,9 @@ __device__ __forceinline__ uint32_t maj3(uint32_t a, uint32_t b, uint32_t c) { r
 #ifndef GOL_RULE8
 #define GOL_RULE8 0
 #endif
+#ifndef GOL_TMIX
+#define GOL_TMIX 0
+#endif
 __device__ __forceinline__ uint32_t life_rule(uint32_t a0, uint32_t a1, uint32_t b0, uint32_t b1,
                                               uint32_t n0, uint32_t n1, uint32_t m)
 {
@@ -518,6 +521,12 @@ __device__ __forceinline__ void march(const MarchArgs &A, uint32_t &flag_alive, 
             const uint32_t nL = mad_lo(x[j], A.four, j ? c4[j - 1] : in4);  // cell x-2 at bit x
             const uint32_t nC = mad_lo(x[j], A.two, j ? c2[j - 1] : in2);   // cell x-1 at bit x (centre)
             const uint32_t nR = x[j];
+#elif GOL_TMIX
+            // timing-only experiment (computes a different automaton): the instruction mix of a
+            // strip-transposed bit layout, where x-neighbours are whole neighbouring words
+            const uint32_t nL = j ? x[j - 1] : left * A.two;
+            const uint32_t nC = x[j];
+            const uint32_t nR = j < kWL - 1 ? x[j + 1] : (right >> (A.four & 1u));
 #else
             const uint32_t nL = shl1_in(j ? x[j - 1] : left, x[j]);
             const uint32_t nC = x[j];
@@ -723,7 +732,13 @@ __global__ void __launch_bounds__(kWarps * 32, K == 8 ? GOL_K8_MINBLOCKS : (K ==
     const ItemMap im = item_map(D, lp.chunk_rows);
     int strip = 0, chunk = 0;
     bool border = false;
-    if (decode_item(im, item, strip, chunk, border)) {
+    // Everything above reads only the launch parameters and the domain descriptor (constant after
+    // upload).  Let the next launch become resident, then wait for the previous one to complete
+    // before touching any grid buffer, flag or scratch word (no-ops without the PDL attribute).
+    asm volatile("griddepcontrol.launch_dependents;");
+    const bool have_item = decode_item(im, item, strip, chunk, border);
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (have_item) {
         ItemCtx c;
         c.in_idx = lp.in_idx; c.out_idx = lp.out_idx; c.seq = lp.seq; c.wait_seq = lp.wait_seq;
         c.signal = lp.signal; c.chunk_rows = lp.chunk_rows; c.skip_mask = 0;
@@ -1041,8 +1056,19 @@ __global__ void popcount_padded_kernel(const uint32_t *__restrict__ pad, int H, 
 template <int K, bool FLAGS>
 cudaError_t launch_strip_t(const GolDomainDev *d, int grid, const GolLaunch &lp, cudaStream_t s)
 {
-    life_strip_kernel<K, FLAGS><<<grid, kWarps * 32, 0, s>>>(d, lp);
-    return cudaGetLastError();
+    // Programmatic dependent launch: the next epoch's CTAs become resident (and run their
+    // prologue) while this epoch drains; they block in griddepcontrol.wait until it has completed.
+    static const bool pdl = [] { const char *v = getenv("GOL_PDL"); return !v || atoi(v) != 0; }();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(kWarps * 32);
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, life_strip_kernel<K, FLAGS>, d, lp);
 }
 
 }  // namespace
