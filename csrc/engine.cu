@@ -263,7 +263,7 @@ bool multi(const gol_engine *e) { return e->P > 1; }
 bool uses_pipe(const gol_engine *e, int k) { return e->pipe_d > 0 && k == e->pipe_lv * e->pipe_d; }
 
 // work items per CTA for depth k (the strip kernel packs 4 items into a CTA, the pipeline kernel 1)
-int items_per_cta(const gol_engine *e, int k) { return uses_pipe(e, k) ? 1 : 4; }
+int items_per_cta(const gol_engine *e, int k) { return uses_pipe(e, k) ? 1 : GOL_STRIP_WARPS; }
 
 int launch_generation_kernel(gol_engine *e, const GolLaunch &lp, int k, int flags)
 {
@@ -415,7 +415,7 @@ int run_epochs(gol_engine *e, int64_t n, int keep, bool want_flags, bool per_gen
             const int64_t items = (int64_t)pp.ndoms * pp.items_per_domain;
             if (pp.items_per_domain <= e->items_cap && e->persist_ctas[kp] > 0) {
                 const int ctas = (int)std::min<int64_t>(e->persist_ctas[kp], gol_div_up(items, 4));
-                pp.total_warps = ctas * 4;
+                pp.total_warps = ctas * GOL_STRIP_WARPS;
                 pp.work_counter = e->d_error + 1;
                 GOL_CUDA(cudaMemsetAsync(pp.work_counter, 0, sizeof(unsigned int), e->stream));
                 GOL_TRY(gol_launch_persistent(e->d_doms, pp, kp, ctas, e->stream));

@@ -61,6 +61,9 @@ static const int GOL_DIR_DX[8] = {0, 0, -1, 1, -1, 1, -1, 1};
 static const int GOL_DIR_OPP[8] = {1, 0, 3, 2, 7, 6, 5, 4};
 
 #define GOL_REC_SLOTS 64  // ring of flag records per process
+#ifndef GOL_STRIP_WARPS
+#define GOL_STRIP_WARPS 4  // warps (= work items) per CTA of the strip, halo and scan kernels
+#endif
 
 struct GolNeighbor {
     uint32_t *buf[GOL_NBUF];   // neighbour's padded buffers (local or peer-mapped)

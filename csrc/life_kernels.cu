@@ -24,7 +24,7 @@
 
 namespace {
 
-constexpr int kWarps = 4;           // warps per CTA
+constexpr int kWarps = GOL_STRIP_WARPS;  // warps per CTA
 constexpr int kWL = 2;              // 32-bit words per lane (64 cells)
 constexpr int kValidLanes = 30;     // lanes 1..30 own output, lanes 0 and 31 are apron
 constexpr int kVW = kValidLanes * kWL;  // owned words per strip
@@ -721,8 +721,13 @@ __device__ __forceinline__ void run_item(const GolDomainDev &D, const ItemCtx &c
 }
 
 template <int K, bool FLAGS>
-__global__ void __launch_bounds__(kWarps * 32, K == 8 ? GOL_K8_MINBLOCKS : (K == 6 ? 4 : 1)) life_strip_kernel(const GolDomainDev *__restrict__ doms,
-                                                                 const GolLaunch lp)
+__global__ void
+#ifdef GOL_MAXNREG
+__maxnreg__(GOL_MAXNREG)
+#else
+__launch_bounds__(kWarps * 32, K == 8 ? GOL_K8_MINBLOCKS : (K == 6 ? 4 : 1))
+#endif
+life_strip_kernel(const GolDomainDev *__restrict__ doms, const GolLaunch lp)
 {
     const int dom_id = blockIdx.x / lp.ctas_per_domain;
     const int cta = blockIdx.x - dom_id * lp.ctas_per_domain;
@@ -1067,7 +1072,9 @@ cudaError_t launch_strip_t(const GolDomainDev *d, int grid, const GolLaunch &lp,
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = pdl ? 1 : 0;
+    // single-domain runs only: with halo flags between domains the early-resident CTAs cost more
+    // than the launch gap they hide (2 GPUs, 16384^2 each: 9.06 us/generation without, 11.1 with)
+    cfg.numAttrs = (pdl && !(lp.signal & 1)) ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, life_strip_kernel<K, FLAGS>, d, lp);
 }
 
