@@ -110,32 +110,52 @@ def bench_ours(args):
         sampler.samples.clear()         # keep only the samples of the timed region
 
     launches0 = life.launch_count
-    dev_ms, gens_done, gens_reported = 0.0, 0, 0
-    # One timed region for all K steps, run the way a serving loop would: the upload of step i+1's
-    # input (pinned host -> device, second stream) overlaps the generation loop of step i.  Every
-    # step still uploads its own input and reads its own result back; the wall clock below covers
-    # all of it (and the L2 flushes).  `value` uses the CUDA-event time of each generation loop.
-    barrier()
-    t0 = time.perf_counter()
-    life.stage_packed(host)
-    for i in range(args.steps):
-        flush.fill_(1)                  # L2 flush between timed iterations
+
+    def timed(steps, do_flush=True, overlap=True, sync_ranks=False):
+        """One timed region for all `steps` steps, run the way a serving loop would: the upload of
+        step i+1's input (pinned host -> device, second stream) overlaps the generation loop of step i.
+        Every step still uploads its own input and reads its own result back; the wall clock covers
+        all of it (and the L2 flushes).  The device time is the CUDA-event time of each generation loop."""
+        dev_ms, gens_done, gens_reported = 0.0, 0, 0
+        barrier()
+        t0 = time.perf_counter()
+        life.stage_packed(host)
+        for i in range(steps):
+            if do_flush:
+                flush.fill_(1)              # L2 flush between timed iterations
+            torch.cuda.synchronize()
+            # staged grid -> padded layout, first halo exchange; next step's H2D starts here and
+            # overlaps this step's loop
+            life.commit_staged(stage_next=host if overlap and i + 1 < steps else None)
+            if sync_ranks:
+                barrier()
+            res = life.run()                # generation loop; reads back flags, generations, population
+            if not overlap and i + 1 < steps:
+                life.stage_packed(host)
+            dev_ms += res.loop_ms           # CUDA events around the generation loop on the engine stream
+            gens_done += res.generations_computed
+            gens_reported = res.generations
+            if os.environ.get("GOL_BENCH_DEBUG"):
+                print(f"step {i}: wall so far {(time.perf_counter() - t0) * 1e3:.2f} ms, loop {res.loop_ms:.2f}", file=sys.stderr)
         torch.cuda.synchronize()
-        life.commit_staged()            # staged grid -> padded layout, first halo exchange
-        if i + 1 < args.steps:
-            life.stage_packed(host)     # next step's H2D, overlapped with this step's loop
-        res = life.run()                # generation loop; reads back flags, generations, population
-        dev_ms += res.loop_ms           # CUDA events around the generation loop on the engine stream
-        gens_done += res.generations_computed
-        gens_reported = res.generations
-        if os.environ.get("GOL_BENCH_DEBUG"):
-            print(f"step {i}: wall so far {(time.perf_counter() - t0) * 1e3:.2f} ms, loop {res.loop_ms:.2f}", file=sys.stderr)
-    torch.cuda.synchronize()
-    e2e_ms = (time.perf_counter() - t0) * 1e3
-    barrier()
+        e2e_ms = (time.perf_counter() - t0) * 1e3
+        barrier()
+        return dev_ms, e2e_ms, gens_done, gens_reported
+
+    dev_ms, e2e_ms, gens_done, gens_reported = timed(args.steps)
     launches = life.launch_count - launches0
     clocks = sampler.stop() if sampler else None
 
+    if os.environ.get("GOL_BENCH_VARIANTS"):   # diagnostics only: which part of a step costs what (stderr)
+        for name, kw in (("default", {}), ("no-flush", {"do_flush": False}), ("serial-stage", {"overlap": False}),
+                         ("rank-barrier-before-run", {"sync_ranks": True}),
+                         ("no-flush,serial,barrier", {"do_flush": False, "overlap": False, "sync_ranks": True})):
+            d, w, _, _ = timed(args.steps, **kw)
+            tv = torch.tensor([d, w], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(tv, op=dist.ReduceOp.MAX)
+            if rank == 0:
+                print(f"[variant] {name}: device {tv[0].item() / args.steps:.3f} ms/step, wall {tv[1].item() / args.steps:.3f} ms/step", file=sys.stderr)
     t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)

@@ -298,6 +298,7 @@ int launch_epoch(gol_engine *e, int k, int in, int out, bool flags, int rec_slot
     static const int dbg = getenv("GOL_DEBUG_COMM") ? atoi(getenv("GOL_DEBUG_COMM")) : 0;  // timing experiments only
     static const int force_signal = getenv("GOL_FORCE_SIGNAL") ? atoi(getenv("GOL_FORCE_SIGNAL")) : 0;
     lp.signal = ((multi(e) || (force_signal & 1)) ? 1 : 0) | (dbg << 8);
+    lp.pdl = multi(e) ? 0 : 1;
     if (force_signal & 2) lp.wait_seq = e->seq - 1;
     if (dbg & 4) lp.wait_seq = 0;
     lp.rec_slot = flags ? rec_slot : -1;
@@ -348,6 +349,7 @@ int autotune_geometry(gol_engine *e, int k, int in, int scratch)
         lp.seq = e->seq;
         lp.wait_seq = 0;
         lp.signal = 3 << 8;  // no pushes, no flags
+        lp.pdl = multi(e) ? 0 : 1;   // same launch mode as the real epochs
         lp.rec_slot = -1;
         GOL_TRY(launch_generation_kernel(e, lp, k, 0));
         GOL_CUDA(cudaEventRecord(e->ev_tune[0], e->stream));

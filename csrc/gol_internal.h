@@ -107,6 +107,7 @@ struct GolLaunch {
     int32_t signal;            // 1: publish epoch flags to neighbours when done
     int32_t rec_slot;          // >=0: publish {alive,diff} record into this slot
     uint32_t rec_seq;
+    int32_t pdl;               // 1: launch with programmatic stream serialisation (single-process runs)
 };
 
 // Persistent (dataflow) launch: `epochs` epochs of K generations in ONE kernel; work items wait

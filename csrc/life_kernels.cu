@@ -1063,7 +1063,7 @@ cudaError_t launch_strip_t(const GolDomainDev *d, int grid, const GolLaunch &lp,
 {
     // Programmatic dependent launch: the next epoch's CTAs become resident (and run their
     // prologue) while this epoch drains; they block in griddepcontrol.wait until it has completed.
-    static const bool pdl = [] { const char *v = getenv("GOL_PDL"); return !v || atoi(v) != 0; }();
+    static const int pdl = [] { const char *v = getenv("GOL_PDL"); return v ? atoi(v) : 1; }();  // 2: also across processes (experiment)
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(kWarps * 32);
@@ -1072,9 +1072,9 @@ cudaError_t launch_strip_t(const GolDomainDev *d, int grid, const GolLaunch &lp,
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    // single-domain runs only: with halo flags between domains the early-resident CTAs cost more
+    // single-process runs only (lp.pdl): with halo flags between GPUs the early-resident CTAs cost more
     // than the launch gap they hide (2 GPUs, 16384^2 each: 9.06 us/generation without, 11.1 with)
-    cfg.numAttrs = (pdl && !(lp.signal & 1)) ? 1 : 0;
+    cfg.numAttrs = ((pdl && lp.pdl) || pdl == 2) ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, life_strip_kernel<K, FLAGS>, d, lp);
 }
 

@@ -202,9 +202,14 @@ class GameOfLife:
         N.check(self._lib.gol_engine_stage_packed(self._h, C.c_void_p(ptr)), "stage_packed")
         return self
 
-    def commit_staged(self) -> "GameOfLife":
-        """Make the staged grid the current one (then run()/step() as after load_packed)."""
+    def commit_staged(self, stage_next=None) -> "GameOfLife":
+        """Make the staged grid the current one (then run()/step() as after load_packed).
+        `stage_next`: start uploading the grid after this one right away (same as calling
+        stage_packed() next, but issued before the ranks synchronise, so the host time of the
+        enqueue does not skew the ranks against each other at the start of the generation loop)."""
         N.check(self._lib.gol_engine_commit_staged(self._h), "commit_staged")
+        if stage_next is not None:
+            self.stage_packed(stage_next)
         self._after_load()
         return self
 

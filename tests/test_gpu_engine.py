@@ -288,7 +288,10 @@ def test_staged_upload(cuda_device):
         life.stage_packed(tb)                      # uploads while the first grid runs
         r1 = life.run()
         assert np.array_equal(life.packed_numpy(), cpu.run(a, w, gen_limit=20)[0]) and r1.generations == 20
-        life.commit_staged()
+        life.commit_staged(stage_next=ta)          # commit b and start re-uploading a in one call
         life.run()
         assert np.array_equal(life.packed_numpy(), cpu.run(b, w, gen_limit=20)[0])
+        life.commit_staged()
+        life.run()
+        assert np.array_equal(life.packed_numpy(), cpu.run(a, w, gen_limit=20)[0])
         life.close()
