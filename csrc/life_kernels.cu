@@ -5,7 +5,7 @@
 //      streams down the rows.  K generations are pipelined in registers (temporal blocking):
 //      level t consumes the row produced by level t-1 one step earlier, so a row is read from
 //      memory once and written once per K generations.  Neighbour words move between lanes
-//      with warp shuffles; the B3/S23 rule is a 10-LOP3 bit-sliced adder per 32 cells.
+//      with warp shuffles; the B3/S23 rule is a 9-LOP3 bit-sliced adder per 32 cells.
 //      The same kernel pushes its border rows/columns straight into the neighbours' ghost
 //      zones (its own for a single torus domain, peer-mapped memory over NVLink otherwise),
 //      publishes release flags, and (FLAGS) reduces the alive / changed bits of the last level.
