@@ -3,6 +3,10 @@
 //   A = third row's sum (0..3) in one of the three 2-bit symmetric encodings; m = centre bit.
 //   out = [A+S == 3] | m & [A+S == 4];   m = 1 implies S >= 1.
 // Question: for which codes does a 3-LOP3 circuit for `out` exist?
+// Result: none when the pair contains the centre row (m = 1 implies S >= 1).  With CARE_A=1 in the
+// environment the single row is the centre row instead (S = above + below, m = 1 implies A >= 1):
+// 36 codes have a 3-gate output stage, but none of those codes can be produced from the two rows
+// in 3 gates, so that form does not beat 7 gates either.
 // usage: pair_search <part> <nparts>
 #include <stdio.h>
 #include <stdlib.h>
@@ -55,7 +59,7 @@ int main(int argc,char**argv){
             int sOf[8]; for(int c=0;c<8;++c) sOf[c]=-1; for(int s=6;s>=0;--s) sOf[code[s]]=s; // 5/6 may share
             tt F=0, care=0;
             for(int i=0;i<64;++i){ int ac=i&3, qc=(i>>2)&7, m=(i>>5)&1; int A=-1; for(int a=0;a<4;++a) if(acode[ae][a]==ac) A=a;
-                int S=sOf[qc]; if(S<0) continue; if(m&&S==0) continue; care|=(tt)1<<i;
+                int S=sOf[qc]; if(S<0) continue; if(getenv("CARE_A") ? (m&&A==0) : (m&&S==0)) continue; care|=(tt)1<<i;
                 // S of a shared code: 5 or 6 both give 0
                 int T=A+S; if(T==3||(T==4&&m)) F|=(tt)1<<i; }
             tt sig[8]; for(int v=0;v<6;++v) sig[v]=VAR[v];
