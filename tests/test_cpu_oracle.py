@@ -143,3 +143,31 @@ def test_topology():
     t2 = Topology(840, 840, 3, 3)
     assert [e[0] for e in (t2.extent(0), t2.extent(1), t2.extent(2))] == [0, 256, 576]
     assert t2.extent(2)[2] == 840 - 576
+
+
+def test_kernel_rule_circuit_truth_table():
+    """The LOP3 circuit of life_rule() in csrc/life_kernels.cu (read from the source) equals B3/S23
+    on all 4*4*4*2 combinations of the three row sums and the centre bit (reference rule: S:60-101)."""
+    import itertools
+    import os
+    import re
+    src = open(os.path.join(os.path.dirname(__file__), "..", "csrc", "life_kernels.cu")).read()
+    body = src[src.index("#else", src.index("life_rule(uint32_t a0")):]
+    body = body[:body.index("#endif")]
+    stmts = re.findall(r"(\w+) = (xor3|maj3|lop3<0x([0-9A-Fa-f]+)>)\((\w+), (\w+), (\w+)\);", body)
+    ret = re.search(r"return lop3<0x([0-9A-Fa-f]+)>\((\w+), (\w+), (\w+)\);", body)
+    assert len(stmts) == 6 and ret, "life_rule is expected to be 7 LOP3"
+
+    def lop3(lut, a, b, c):
+        return (lut >> ((a << 2) | (b << 1) | c)) & 1
+
+    for A, B, Nn, m in itertools.product(range(4), range(4), range(4), range(2)):
+        if m and B == 0:
+            continue   # the middle row sum includes the centre cell
+        env = {"a0": A & 1, "a1": A >> 1, "b0": B & 1, "b1": B >> 1, "n0": Nn & 1, "n1": Nn >> 1, "m": m}
+        for name, fn, lut, x, y, z in stmts:
+            l = 0x96 if fn == "xor3" else 0xE8 if fn == "maj3" else int(lut, 16)
+            env[name] = lop3(l, env[x], env[y], env[z])
+        out = lop3(int(ret.group(1), 16), env[ret.group(2)], env[ret.group(3)], env[ret.group(4)])
+        T = A + B + Nn
+        assert out == int(T == 3 or (T == 4 and m)), (A, B, Nn, m)
