@@ -5,7 +5,7 @@
 //      streams down the rows.  K generations are pipelined in registers (temporal blocking):
 //      level t consumes the row produced by level t-1 one step earlier, so a row is read from
 //      memory once and written once per K generations.  Neighbour words move between lanes
-//      with warp shuffles; the B3/S23 rule is a 9-LOP3 bit-sliced adder per 32 cells.
+//      with warp shuffles; the B3/S23 rule is an 8-LOP3 bit-sliced adder per 32 cells.
 //      The same kernel pushes its border rows/columns straight into the neighbours' ghost
 //      zones (its own for a single torus domain, peer-mapped memory over NVLink otherwise),
 //      publishes release flags, and (FLAGS) reduces the alive / changed bits of the last level.
@@ -51,20 +51,19 @@ __device__ __forceinline__ uint32_t maj3(uint32_t a, uint32_t b, uint32_t c) { r
 // Next state of 32 cells from the bit-sliced 3-cell row sums (s0 + 2*s1, centre included) of
 // the rows above (a), at (b) and below (n) and the centre word m.  T = 9-cell sum:
 // alive' = (T == 3) | (m & T == 4).
-// Seven LOP3: the column of low bits is encoded as (parity, all-equal) instead of (parity, carry);
-// with that encoding the remaining 5-input function has a 3-gate realisation (found by the
-// exhaustive search in scripts/search/lop3_search.c; none exists for the (parity, carry) encoding,
-// and no 2-gate one for any encoding).  GOL_RULE8 keeps the former 8-gate form for comparison.
-#ifndef GOL_RULE8
-#define GOL_RULE8 0
-#endif
-#ifndef GOL_TMIX
-#define GOL_TMIX 0
+// Six LOP3, found by exact synthesis (scripts/search/exact_synth.py, z3): the circuit is only
+// required to be right where the centre bit is consistent with its row sum (m = 1 implies the
+// middle sum b >= 1, which holds by construction because b includes the centre cell); it differs
+// from the rule on two impossible inputs only ((a, b, n, m) = (0, 0, 0, 1) and (2, 0, 2, 1)).  Former forms, kept
+// for comparison: GOL_RULE=7 (parity / all-equal encoding of the low column + 3 gates, found by
+// scripts/search/lop3_search.c) and GOL_RULE=8 (two full adders + 4 gates).
+#ifndef GOL_RULE
+#define GOL_RULE 6
 #endif
 __device__ __forceinline__ uint32_t life_rule(uint32_t a0, uint32_t a1, uint32_t b0, uint32_t b1,
                                               uint32_t n0, uint32_t n1, uint32_t m)
 {
-#if GOL_RULE8
+#if GOL_RULE == 8
     const uint32_t x0 = xor3(a0, b0, n0);
     const uint32_t k0 = maj3(a0, b0, n0);
     const uint32_t x1 = xor3(a1, b1, n1);
@@ -73,7 +72,7 @@ __device__ __forceinline__ uint32_t life_rule(uint32_t a0, uint32_t a1, uint32_t
     const uint32_t h = lop3<0x42>(k0, x1, k1);   // ~(k0 ^ x1) & (k1 ^ (k0&x1)) : T in {4,5}
     const uint32_t u = lop3<0x08>(x0, h, m);     // ~x0 & h & m                 : T == 4, alive
     return lop3<0xEA>(x0, g, u);                 // (x0 & g) | u
-#else
+#elif GOL_RULE == 7
     const uint32_t p0 = xor3(a0, b0, n0);        // low column: count odd
     const uint32_t e0 = lop3<0x81>(a0, b0, n0);  // low column: count 0 or 3
     const uint32_t p1 = xor3(a1, b1, n1);        // high column: count odd
@@ -81,6 +80,13 @@ __device__ __forceinline__ uint32_t life_rule(uint32_t a0, uint32_t a1, uint32_t
     const uint32_t g1 = lop3<0x56>(p0, e0, k1);
     const uint32_t g2 = lop3<0xA4>(p0, m, g1);
     return lop3<0x60>(g2, e0, p1);
+#else
+    const uint32_t p0 = xor3(a0, b0, n0);        // low column: count odd
+    const uint32_t d0 = lop3<0x7E>(a0, b0, n0);  // low column: count 1 or 2
+    const uint32_t o1 = lop3<0x16>(a1, b1, n1);  // high column: count exactly 1
+    const uint32_t w = maj3(a1, n0, n1);         // (no symmetric meaning; part of the synthesised circuit)
+    const uint32_t g = lop3<0x76>(w, o1, d0);
+    return lop3<0x54>(m, p0, g);
 #endif
 }
 

@@ -23,6 +23,7 @@ for A, B, Nn, m in itertools.product(range(4), range(4), range(4), range(2)):
 NI = 7
 s = z3.SolverFor("QF_FD")
 s.set("timeout", tmo * 1000)
+s.set("sat.random_seed", 7)
 sel = [[[z3.Bool(f"s_{i}_{k}_{j}") for j in range(NI + i)] for k in range(3)] for i in range(NG)]
 lut = [[z3.Bool(f"l_{i}_{b}") for b in range(8)] for i in range(NG)]
 val = [[z3.Bool(f"v_{i}_{r}") for r in range(len(rows))] for i in range(NG)]
@@ -47,6 +48,10 @@ for i in range(NG):
             cond = [op[i][0][r] if b & 4 else z3.Not(op[i][0][r]), op[i][1][r] if b & 2 else z3.Not(op[i][1][r]),
                     op[i][2][r] if b & 1 else z3.Not(op[i][2][r])]
             s.add(z3.Implies(z3.And(*cond), val[i][r] == lut[i][b]))
+# every gate depends on each of its three operands
+for i in range(NG):
+    for k, bit in enumerate((4, 2, 1)):
+        s.add(z3.Or([z3.Xor(lut[i][b], lut[i][b | bit]) for b in range(8) if not b & bit]))
 # every gate but the last is used by a later gate
 for i in range(NG - 1):
     s.add(z3.Or([sel[i2][k][NI + i] for i2 in range(i + 1, NG) for k in range(3)]))

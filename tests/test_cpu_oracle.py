@@ -156,7 +156,7 @@ def test_kernel_rule_circuit_truth_table():
     body = body[:body.index("#endif")]
     stmts = re.findall(r"(\w+) = (xor3|maj3|lop3<0x([0-9A-Fa-f]+)>)\((\w+), (\w+), (\w+)\);", body)
     ret = re.search(r"return lop3<0x([0-9A-Fa-f]+)>\((\w+), (\w+), (\w+)\);", body)
-    assert len(stmts) == 6 and ret, "life_rule is expected to be 7 LOP3"
+    assert len(stmts) == 5 and ret, "life_rule is expected to be 6 LOP3"
 
     def lop3(lut, a, b, c):
         return (lut >> ((a << 2) | (b << 1) | c)) & 1
