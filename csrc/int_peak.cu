@@ -51,18 +51,17 @@ __global__ void __launch_bounds__(256) pipe_kernel(unsigned *out, unsigned seed)
                 asm volatile("lop3.b32 %0, %0, %1, %2, 0x14;" : "+r"(v[j]) : "r"(a), "r"(b));
                 asm volatile("lop3.b32 %0, %0, %1, %2, 0x42;" : "+r"(v[j]) : "r"(a), "r"(b));
                 asm volatile("lop3.b32 %0, %0, %1, %2, 0xEA;" : "+r"(v[j]) : "r"(a), "r"(b));
-            } else if (MODE == 8) {  // the generation kernel's mix: 2 SHF + 9 LOP3 per 32 x 32 cells
+            } else if (MODE == 8) {  // the generation kernel's mix: 2 SHF + 8 LOP3 per 32 x 32 cells
                 asm volatile("shf.l.wrap.b32 %0, %1, %0, 1;" : "+r"(v[j]) : "r"(a));
                 asm volatile("shf.r.wrap.b32 %0, %0, %1, 1;" : "+r"(v[j]) : "r"(b));
                 asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(v[j]) : "r"(a), "r"(b));
                 asm volatile("lop3.b32 %0, %0, %1, %2, 0xE8;" : "+r"(v[j]) : "r"(a), "r"(b));
-                asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(v[j]) : "r"(a), "r"(b));
-                asm volatile("lop3.b32 %0, %0, %1, %2, 0x81;" : "+r"(v[j]) : "r"(a), "r"(b));
                 asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(v[j]) : "r"(b), "r"(a));
+                asm volatile("lop3.b32 %0, %0, %1, %2, 0x7E;" : "+r"(v[j]) : "r"(a), "r"(b));
+                asm volatile("lop3.b32 %0, %0, %1, %2, 0x16;" : "+r"(v[j]) : "r"(b), "r"(a));
                 asm volatile("lop3.b32 %0, %0, %1, %2, 0xE8;" : "+r"(v[j]) : "r"(b), "r"(a));
-                asm volatile("lop3.b32 %0, %0, %1, %2, 0x56;" : "+r"(v[j]) : "r"(a), "r"(b));
-                asm volatile("lop3.b32 %0, %0, %1, %2, 0xA4;" : "+r"(v[j]) : "r"(a), "r"(b));
-                asm volatile("lop3.b32 %0, %0, %1, %2, 0x60;" : "+r"(v[j]) : "r"(a), "r"(b));
+                asm volatile("lop3.b32 %0, %0, %1, %2, 0x76;" : "+r"(v[j]) : "r"(a), "r"(b));
+                asm volatile("lop3.b32 %0, %0, %1, %2, 0x54;" : "+r"(v[j]) : "r"(a), "r"(b));
             } else if (MODE == 4) {  // former kernel mix: 5 LOP3 + 1 SHF per chain step (= 10:2)
                 asm volatile("shf.l.wrap.b32 %0, %1, %0, 1;" : "+r"(v[j]) : "r"(a));
                 asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(v[j]) : "r"(a), "r"(b));
@@ -96,7 +95,7 @@ double run(int sms, int clock_khz, double *ms_out)
     CHECK(cudaEventSynchronize(e1));
     float ms;
     CHECK(cudaEventElapsedTime(&ms, e0, e1));
-    const int per_step = MODE == 8 ? 11 : (MODE == 4 || MODE == 7) ? 6 : (MODE == 6 ? 2 : 1);
+    const int per_step = MODE == 8 ? 10 : (MODE == 4 || MODE == 7) ? 6 : (MODE == 6 ? 2 : 1);
     const double warp_instr = (double)reps * blocks * 8.0 * kIters * kChains * per_step;
     const double cycles = ms * 1e-3 * clock_khz * 1e3;
     *ms_out = ms / reps;
@@ -119,17 +118,17 @@ int main()
     const double imadhi = run<5>(p.multiProcessorCount, clock_khz, &ms[5]);
     const double imadwide = run<6>(p.multiProcessorCount, clock_khz, &ms[6]);
     const double mix_imad = run<7>(p.multiProcessorCount, clock_khz, &ms[7]);
-    const double mix92 = run<8>(p.multiProcessorCount, clock_khz, &ms[8]);
-    // the generation kernel needs 11 ALU-pipe warp-instructions per 32 lanes x 32 cells (2 SHF + 9 LOP3;
-    // 12 = 2 + 10 before the rule was reduced to 7 LOP3)
-    const double cells_per_s = mix92 * p.multiProcessorCount * (clock_khz * 1e3) * 1024.0 / 11.0;
+    const double mix82 = run<8>(p.multiProcessorCount, clock_khz, &ms[8]);
+    // the generation kernel needs 10 ALU-pipe warp-instructions per 32 lanes x 32 cells (2 SHF + 8 LOP3;
+    // 12 = 2 + 10 with the 8-LOP3 rule it started with)
+    const double cells_per_s = mix82 * p.multiProcessorCount * (clock_khz * 1e3) * 1024.0 / 10.0;
     const double cells_per_s_12 = mix * p.multiProcessorCount * (clock_khz * 1e3) * 1024.0 / 12.0;
     printf("{\"gpu\": \"%s\", \"sms\": %d, \"clock_mhz_nominal_max\": %.0f, "
-           "\"warp_instr_per_clk_per_sm\": {\"lop3\": %.3f, \"shf\": %.3f, \"imad\": %.3f, \"shfl\": %.3f, \"lop3_shf_mix_9_2\": %.3f, \"lop3_shf_mix_10_2\": %.3f, \"imad_hi\": %.3f, \"imad_wide_plus_iadd\": %.3f, \"lop3_imad_mix_10_2\": %.3f}, "
+           "\"warp_instr_per_clk_per_sm\": {\"lop3\": %.3f, \"shf\": %.3f, \"imad\": %.3f, \"shfl\": %.3f, \"lop3_shf_mix_8_2\": %.3f, \"lop3_shf_mix_10_2\": %.3f, \"imad_hi\": %.3f, \"imad_wide_plus_iadd\": %.3f, \"lop3_imad_mix_10_2\": %.3f}, "
            "\"note\": \"rates assume the nominal max SM clock; 2.0 = 64 lanes/clk/SM\", "
-           "\"int_roofline_cell_updates_per_s_at_11_alu_ops_per_32_cells\": %.4g, "
+           "\"int_roofline_cell_updates_per_s_at_10_alu_ops_per_32_cells\": %.4g, "
            "\"int_roofline_cell_updates_per_s_at_12_alu_ops_per_32_cells\": %.4g}\n",
-           p.name, p.multiProcessorCount, clock_khz / 1e3, lop3, shf, imad, shfl, mix92, mix, imadhi, imadwide, mix_imad,
+           p.name, p.multiProcessorCount, clock_khz / 1e3, lop3, shf, imad, shfl, mix82, mix, imadhi, imadwide, mix_imad,
            cells_per_s, cells_per_s_12);
     return 0;
 }
