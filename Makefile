@@ -10,7 +10,7 @@
 NVCC      ?= nvcc
 CXX       ?= g++
 ARCH      := -gencode arch=compute_100a,code=sm_100a
-NVFLAGS   := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC,-Wall,-Wno-unused-function -Xptxas -v
+NVFLAGS   := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC,-Wall,-Wno-unused-function -Xptxas -v $(EXTRA_NVFLAGS)
 CXXFLAGS  := -O3 -std=c++17 -fPIC -Wall -pthread
 BUILD     := build
 LIB       := libgolb200.so
