@@ -51,7 +51,6 @@ struct ArenaLayout {
     std::vector<int64_t> buf_off;     // [local domain][GOL_NBUF] byte offsets
     std::vector<int64_t> flags_off;   // [local domain]
     std::vector<int64_t> scratch_off; // [local domain]
-    std::vector<int64_t> items_off;   // [local domain] per-item epoch flags (persistent kernel)
     int64_t rec_off = 0;
     int64_t total = 0;
 };
@@ -88,21 +87,26 @@ struct gol_engine {
     cudaStream_t copy_stream = nullptr;  // staged (overlapped) uploads run here
     cudaEvent_t ev_staged = nullptr, ev_stage_free = nullptr;
     bool staged = false, stage_busy = false;
-    int max_strips = 1;
+    int max_strips = 1, max_strips_ext = 1;  // strips per row: plain / with the ghost words of a deep-halo epoch
     int64_t max_h = 1;
-    int64_t items_cap = 0;          // per-domain capacity of the item flag array
-    bool use_persistent = false;    // GOL_PERSISTENT=1: one dataflow launch per batch instead of one per epoch
-    int persist_ctas[9] = {0};
     int tuned_rows[17] = {0};       // measured best chunk height per temporal depth (0 = not tuned yet)
-    int pipe_lv = 0, pipe_d = 0;    // GOL_PIPE=LVxD: warp-pipelined kernel for epochs of LV*D generations
-    bool autotune = true;           // GOL_AUTOTUNE=0 disables the one-off geometry timing      // max co-resident CTAs of the persistent kernel per k (0 = not queried)
+    bool autotune = true;           // GOL_AUTOTUNE=0 disables the one-off geometry timing
+    bool deep_halo = false;         // epochs run as pairs with one 16-deep halo exchange per pair (see run_epochs)
+    bool pdl_multi = false;         // GOL_PDL=2: programmatic dependent launch also between processes
+    long long wait_timeout = 0;     // device-side flag waits give up after this many clock cycles
+    // GOL_TRACE=<n>: per-launch timeline records (first CTA start, last CTA end, flag spin cycles)
+    GolTrace *d_trace = nullptr;
+    int trace_cap = 0, trace_n = 0;
+    std::vector<int> trace_meta;    // per record: k | mode << 8 | flags << 16
+    uint64_t *scratch_dense = nullptr;  // engine-owned dense scratch (largest local domain): randomize, population
+    unsigned long long *d_count = nullptr;
 
     // dense path (tiny grids, single domain)
     uint64_t *dense[3] = {nullptr, nullptr, nullptr};
     uint32_t *d_dflags = nullptr;  // [kMaxBatch + 1][2]
     uint32_t *h_dflags = nullptr;  // pinned
 
-    int cur = 0, prev_in = -1;
+    int cur = 0, hist[2] = {-1, -1};  // current buffer; inputs of the last two epochs
     uint32_t seq = 0, rec_seq = 0;
     bool prepared = false;
     int64_t launches = 0;
@@ -141,7 +145,6 @@ int build_arena_layout(const gol_engine *e, int p, ArenaLayout *A)
     A->buf_off.assign((size_t)e->per_proc * GOL_NBUF, 0);
     A->flags_off.assign((size_t)e->per_proc, 0);
     A->scratch_off.assign((size_t)e->per_proc, 0);
-    A->items_off.assign((size_t)e->per_proc, 0);
     int64_t off = 0;
     for (int i = 0; i < e->per_proc; ++i) {
         const int gid = p * e->per_proc + i;
@@ -159,8 +162,6 @@ int build_arena_layout(const gol_engine *e, int p, ArenaLayout *A)
         off += 256;
         A->scratch_off[(size_t)i] = off;
         off += 256;
-        A->items_off[(size_t)i] = off;
-        off = align_up(off + (int64_t)e->items_cap * 4, 256);
     }
     A->rec_off = off;
     off = align_up(off + (int64_t)GOL_REC_SLOTS * e->ndom * 8, 256);
@@ -192,16 +193,13 @@ int upload_domains(gol_engine *e)
         D.nwf32 = 2 * ld.L.nqf;
         D.rem = ld.L.rem;
         D.pitch32 = ld.L.pitch32;
-        D.strips = ld.strips;
         D.global_id = ld.gid;
         D.epoch_flags = reinterpret_cast<uint32_t *>(e->arena + A.flags_off[(size_t)i]);
         D.scratch = reinterpret_cast<GolScratch *>(e->arena + A.scratch_off[(size_t)i]);
-        D.item_flags = reinterpret_cast<uint32_t *>(e->arena + A.items_off[(size_t)i]);
         D.rec_tables = e->d_rec_tables;
         D.proc_count = e->P;
         D.num_domains = e->ndom;
-        D.mul2 = 2;
-        D.mul4 = 4;
+        D.wait_timeout = e->wait_timeout;
         for (int d = 0; d < GOL_NDIR; ++d) {
             const int ngid = neighbor_gid(e, ld.gid, d);
             if (ngid == ld.gid) D.self_mask |= 1u << d;
@@ -228,53 +226,39 @@ int upload_domains(gol_engine *e)
     return 0;
 }
 
-// Launch geometry for temporal depth k: chunk height trades apron redundancy (2k rows per
-// chunk) against the number of independent warps.
-bool uses_pipe(const gol_engine *e, int k);
-int items_per_cta(const gol_engine *e, int k);
-
-void geometry(const gol_engine *e, int k, GolLaunch *lp, int resident_warps_per_sm = 0)
-{
-    static const int env_warps = getenv("GOL_WARPS_PER_SM") ? atoi(getenv("GOL_WARPS_PER_SM")) : 0;
-    if (!env_warps && !resident_warps_per_sm && k <= 16 && e->tuned_rows[k] > 0) {
-        const int64_t rows = e->tuned_rows[k], chunks = gol_div_up(e->max_h, rows);
-        lp->chunk_rows = (int32_t)rows;
-        lp->chunks = (int32_t)chunks;
-        lp->ctas_per_domain = (int32_t)gol_div_up(chunks * e->max_strips, items_per_cta(e, k));
-        return;
-    }
-    const int warps_per_sm = env_warps ? env_warps : (resident_warps_per_sm ? resident_warps_per_sm : 16);
-    const int64_t target_items = (int64_t)e->num_sms * warps_per_sm / std::max(1, e->per_proc);
-    // classic launches round up (a few CTAs more than slots is harmless); the persistent kernel
-    // must not exceed its resident warps, or some warps would carry two items per epoch
-    int64_t chunks = resident_warps_per_sm ? std::max<int64_t>(1, target_items / e->max_strips)
-                                           : std::max<int64_t>(1, (target_items + e->max_strips - 1) / e->max_strips);
-    int64_t rows = gol_div_up(e->max_h, chunks);
-    const int64_t min_rows = std::min<int64_t>(e->max_h, std::max<int64_t>(8, 6 * k));
-    if (rows < min_rows) rows = min_rows;
-    chunks = gol_div_up(e->max_h, rows);
-    lp->chunk_rows = (int32_t)rows;
-    lp->chunks = (int32_t)chunks;
-    lp->ctas_per_domain = (int32_t)gol_div_up(chunks * e->max_strips, items_per_cta(e, k));
-}
-
 bool multi(const gol_engine *e) { return e->P > 1; }
 
-bool uses_pipe(const gol_engine *e, int k) { return e->pipe_d > 0 && k == e->pipe_lv * e->pipe_d; }
-
-// work items per CTA for depth k (the strip kernel packs 4 items into a CTA, the pipeline kernel 1)
-int items_per_cta(const gol_engine *e, int k) { return uses_pipe(e, k) ? 1 : GOL_STRIP_WARPS; }
-
-int launch_generation_kernel(gol_engine *e, const GolLaunch &lp, int k, int flags)
+// Launch geometry for temporal depth k.  Every domain is cut into a first and a last chunk of
+// GOL_EDGE_ROWS rows (the rows that are exchanged with the north / south neighbours; short, so that
+// they are done early in the launch) and interior chunks whose height trades apron redundancy
+// (2k rows of pipeline fill per chunk) against the number of independent warps.
+// `rows` > 0 forces the interior chunk height (autotune); ext_y / ext_x: deep-halo epoch.
+void geometry(const gol_engine *e, int k, GolLaunch *lp, int ext_y = 0, int ext_x = 0, int rows = 0)
 {
-    if (uses_pipe(e, k)) return gol_launch_pipe(e->d_doms, e->per_proc, lp, e->pipe_lv, e->pipe_d, flags, e->stream);
-    return gol_launch_strip(e->d_doms, e->per_proc, lp, k, flags, e->stream);
+    static const int env_warps = getenv("GOL_WARPS_PER_SM") ? atoi(getenv("GOL_WARPS_PER_SM")) : 0;
+    const int E = GOL_EDGE_ROWS;
+    const int64_t S = ext_x ? e->max_strips_ext : e->max_strips;
+    const int64_t span = e->max_h + 2 * ext_y;
+    const bool single = span < 3 * E;
+    const int64_t interior = single ? span : span - 2 * E;
+    lp->edge_rows = E;
+    lp->ext_y = ext_y;
+    lp->ext_x = ext_x;
+    if (!rows && !env_warps && k <= 16 && e->tuned_rows[k] > 0) rows = e->tuned_rows[k];
+    if (!rows) {
+        const int warps_per_sm = env_warps ? env_warps : 12;
+        const int64_t target_items = (int64_t)e->num_sms * warps_per_sm / std::max(1, e->per_proc);
+        const int64_t chunks = std::max<int64_t>(1, gol_div_up(target_items, S) - (single ? 0 : 2));
+        rows = (int)std::max<int64_t>(gol_div_up(interior, chunks), std::min<int64_t>(interior, std::max(8, 6 * k)));
+    }
+    lp->chunk_rows = rows;
+    const int64_t items = single ? S : (2 + gol_div_up(interior, rows)) * S;
+    lp->ctas_per_domain = (int32_t)gol_div_up(items, GOL_STRIP_WARPS);
 }
 
 // largest temporal depth the strip kernel is instantiated for that does not exceed cap
-int pick_depth(int64_t cap, const gol_engine *e = nullptr)
+int pick_depth(int64_t cap)
 {
-    if (e && e->pipe_d > 0 && e->kmax == e->pipe_lv * e->pipe_d && cap >= e->kmax) return e->kmax;
     if (cap >= 16) return 16;
     if (cap >= 8) return 8;
     return (int)std::max<int64_t>(1, cap);
@@ -286,24 +270,39 @@ int check_ready(gol_engine *e, const char *what)
     return 0;
 }
 
+GolTrace *next_trace(gol_engine *e, int k, int mode, bool flags)
+{
+    if (!e->d_trace || e->trace_n >= e->trace_cap) return nullptr;
+    e->trace_meta.push_back(k | (mode << 8) | ((flags ? 1 : 0) << 16));
+    return e->d_trace + e->trace_n++;
+}
+
+// Epoch kinds.  CLASSIC waits for the neighbours' pushes of the previous epoch and pushes its own
+// borders.  A deep-halo pair exchanges halos once per two epochs: PAIR_FIRST waits, also computes
+// the k ghost rows / 64 ghost cells next to the domain from the 16-row / 128-cell deep ghost zone,
+// and pushes nothing; PAIR_SECOND needs no remote data and pushes a full-depth halo.
+enum EpochMode { CLASSIC = 0, PAIR_FIRST = 1, PAIR_SECOND = 2 };
+
 // one strip-kernel epoch: k generations from buffer `in` to buffer `out`
-int launch_epoch(gol_engine *e, int k, int in, int out, bool flags, int rec_slot, uint32_t rec_seq)
+int launch_epoch(gol_engine *e, int k, int in, int out, bool flags, int rec_slot, uint32_t rec_seq, EpochMode mode)
 {
     GolLaunch lp{};
-    geometry(e, k, &lp);
+    const int ext = mode == PAIR_FIRST ? k : 0;
+    geometry(e, k, &lp, ext, ext ? 2 : 0);
     lp.in_idx = in;
     lp.out_idx = out;
-    lp.wait_seq = multi(e) ? e->seq : 0;
-    lp.seq = ++e->seq;
     static const int dbg = getenv("GOL_DEBUG_COMM") ? atoi(getenv("GOL_DEBUG_COMM")) : 0;  // timing experiments only
-    static const int force_signal = getenv("GOL_FORCE_SIGNAL") ? atoi(getenv("GOL_FORCE_SIGNAL")) : 0;
-    lp.signal = ((multi(e) || (force_signal & 1)) ? 1 : 0) | (dbg << 8);
-    lp.pdl = multi(e) ? 0 : 1;
-    if (force_signal & 2) lp.wait_seq = e->seq - 1;
-    if (dbg & 4) lp.wait_seq = 0;
+    lp.wait_seq = (multi(e) && mode != PAIR_SECOND && !(dbg & 4)) ? e->seq : 0;
+    lp.push = (mode != PAIR_FIRST ? (multi(e) ? 3 : 1) : 0) | ((dbg & 3) << 8);
+    lp.seq = mode != PAIR_FIRST ? ++e->seq : e->seq;
+    lp.push_rows = G;
+    // waiting items go last (the neighbours' flags have a whole epoch to arrive), pushing items first
+    lp.border_last = mode == PAIR_FIRST ? 1 : 0;
+    lp.pdl = (!multi(e) || e->pdl_multi) ? 1 : 0;
     lp.rec_slot = flags ? rec_slot : -1;
     lp.rec_seq = rec_seq;
-    GOL_TRY(launch_generation_kernel(e, lp, k, flags ? 1 : 0));
+    lp.trace = next_trace(e, k, mode, flags);
+    GOL_TRY(gol_launch_strip(e->d_doms, e->per_proc, lp, k, flags ? 1 : 0, e->stream));
     ++e->launches;
     return 0;
 }
@@ -315,45 +314,43 @@ int launch_epoch(gol_engine *e, int k, int in, int out, bool flags, int rec_slot
 int autotune_geometry(gol_engine *e, int k, int in, int scratch)
 {
     if (k > 16 || e->tuned_rows[k] || e->max_h < 256) return 0;
+    const int64_t interior = e->max_h - 2 * GOL_EDGE_ROWS;
+    const int min_rows = std::max(8, 2 * k);
     std::vector<int> cands;
+    auto add = [&](int64_t rows) {
+        if (rows < min_rows || rows > interior) return;
+        if (std::find(cands.begin(), cands.end(), (int)rows) == cands.end()) cands.push_back((int)rows);
+    };
     for (int w = 10; w <= 26; ++w) {
         const int64_t target = (int64_t)e->num_sms * w / std::max(1, e->per_proc);
-        int64_t chunks = std::max<int64_t>(1, gol_div_up(target, e->max_strips));
-        int64_t rows = std::max<int64_t>(gol_div_up(e->max_h, chunks), std::min<int64_t>(e->max_h, std::max(8, 4 * k)));
-        if (std::find(cands.begin(), cands.end(), (int)rows) == cands.end()) cands.push_back((int)rows);
+        add(gol_div_up(interior, std::max<int64_t>(1, gol_div_up(target, e->max_strips) - 2)));
     }
     // heights that fill the machine exactly: m full waves of resident CTAs, no partial last wave
     int occ = 0;
-    const bool pipe = uses_pipe(e, k);
-    if ((pipe ? gol_pipe_ctas_per_sm(e->pipe_lv, e->pipe_d, &occ) : gol_strip_ctas_per_sm(k, &occ)) == 0 && occ > 0) {
-        const int64_t slots = (int64_t)e->num_sms * occ * items_per_cta(e, k) / std::max(1, e->per_proc);  // resident work items
+    if (gol_strip_ctas_per_sm(k, &occ) == 0 && occ > 0) {
+        const int64_t slots = (int64_t)e->num_sms * occ * GOL_STRIP_WARPS / std::max(1, e->per_proc);  // resident work items
         for (int m = 1; m <= 3; ++m) {
-            const int64_t chunks = m * slots / e->max_strips;
+            const int64_t chunks = m * slots / e->max_strips - 2;
             if (chunks < 1) continue;
-            for (int extra = 0; extra <= 1; ++extra) {
-                const int64_t rows = gol_div_up(e->max_h, chunks) + extra;
-                if (rows < std::max(8, 2 * k) || rows > e->max_h) continue;
-                if (std::find(cands.begin(), cands.end(), (int)rows) == cands.end()) cands.push_back((int)rows);
-            }
+            for (int extra = 0; extra <= 1; ++extra) add(gol_div_up(interior, chunks) + extra);
         }
     }
     float best = 1e30f;
     int best_rows = 0;
     auto time_rows = [&](int rows, float *ms_out) -> int {
         GolLaunch lp{};
-        lp.chunk_rows = rows;
-        lp.chunks = (int32_t)gol_div_up(e->max_h, rows);
-        lp.ctas_per_domain = (int32_t)gol_div_up((int64_t)lp.chunks * e->max_strips, items_per_cta(e, k));
+        geometry(e, k, &lp, 0, 0, rows);
         lp.in_idx = in;
         lp.out_idx = scratch;
         lp.seq = e->seq;
         lp.wait_seq = 0;
-        lp.signal = 3 << 8;  // no pushes, no flags
-        lp.pdl = multi(e) ? 0 : 1;   // same launch mode as the real epochs
+        lp.push = 0;                 // no pushes, no flags
+        lp.push_rows = G;
+        lp.pdl = (!multi(e) || e->pdl_multi) ? 1 : 0;   // same launch mode as the real epochs
         lp.rec_slot = -1;
-        GOL_TRY(launch_generation_kernel(e, lp, k, 0));
+        GOL_TRY(gol_launch_strip(e->d_doms, e->per_proc, lp, k, 0, e->stream));
         GOL_CUDA(cudaEventRecord(e->ev_tune[0], e->stream));
-        for (int i = 0; i < 3; ++i) GOL_TRY(launch_generation_kernel(e, lp, k, 0));
+        for (int i = 0; i < 3; ++i) GOL_TRY(gol_launch_strip(e->d_doms, e->per_proc, lp, k, 0, e->stream));
         GOL_CUDA(cudaEventRecord(e->ev_tune[1], e->stream));
         GOL_CUDA(cudaEventSynchronize(e->ev_tune[1]));
         e->launches += 4;
@@ -371,7 +368,7 @@ int autotune_geometry(gol_engine *e, int k, int in, int scratch)
     const int centre = best_rows;
     for (int d = -3; d <= 3; ++d) {
         const int rows = centre + d;
-        if (d == 0 || rows < std::max(8, 2 * k) || rows > e->max_h) continue;
+        if (d == 0 || rows < min_rows || rows > interior) continue;
         if (std::find(cands.begin(), cands.end(), rows) != cands.end()) continue;
         float ms = 0;
         GOL_TRY(time_rows(rows, &ms));
@@ -381,65 +378,46 @@ int autotune_geometry(gol_engine *e, int k, int in, int scratch)
     return 0;
 }
 
-// Run n generations starting from e->cur as epochs of at most kmax; buffers `keep` is never
+// Output buffer of the next epoch.  Never the epoch's input nor a checkpoint.  Between processes
+// a rank may run ahead of its neighbours: its pushes land in the neighbour's buffer of the same
+// index while that neighbour is still up to two epochs behind (deep-halo pairs: the pushing epoch
+// follows an epoch that waited for pushes made two epochs earlier), so the inputs of the last
+// two epochs are excluded as well - four rotating buffers.
+int pick_out(const gol_engine *e, int in, int keep, int keep2, int *out)
+{
+    for (int relax = 0; relax <= (multi(e) ? 0 : 2); ++relax)
+        for (int i = 0; i < GOL_NBUF; ++i) {
+            if (i == in || i == keep || i == keep2) continue;
+            if (relax < 2 && i == e->hist[0]) continue;
+            if (relax < 1 && i == e->hist[1]) continue;
+            *out = i;
+            return 0;
+        }
+    GOL_FAIL("internal error: no free grid buffer for the next epoch");
+}
+
+// Run n generations starting from e->cur as epochs of at most kcap; buffers `keep`/`keep2` are never
 // written.  With want_flags the last epoch publishes a record (rec slot/seq returned).
 int run_epochs(gol_engine *e, int64_t n, int keep, bool want_flags, bool per_gen_flags, int kcap, int keep2 = -1)
 {
-    // Output buffers rotate over the buffers that are neither the epoch's input, nor the
-    // previous epoch's input (a neighbouring rank may still be reading it: flags are published
-    // as soon as the border items are done, not at the end of the launch), nor `keep`.
     int in = e->cur;
     int64_t left = n;
-
-    // Leading run of full-depth epochs: one persistent (dataflow) launch instead of one launch
-    // per epoch.  The flagged last epoch of a batch and remainder epochs stay classic launches.
-    if (!per_gen_flags && e->use_persistent) {
-        const int kp = pick_depth(std::min<int64_t>(left, kcap), e);
-        int64_t count = left / kp;
-        if (want_flags && count * kp == left) --count;
-        int rot[3], nrot = 0;
-        for (int i = 0; i < GOL_NBUF; ++i)
-            if (i != in && i != keep && i != keep2 && i != e->prev_in && nrot < 3) rot[nrot++] = i;
-        if (e->prev_in >= 0 && e->prev_in != in && e->prev_in != keep && e->prev_in != keep2 && nrot < 3) rot[nrot++] = e->prev_in;  // written last
-        if (count >= 2 && (kp == 1 || kp == 2 || kp == 4 || kp == 8) && nrot == 3) {
-            if (!e->persist_ctas[kp]) GOL_TRY(gol_persistent_max_ctas(kp, e->cfg.device, &e->persist_ctas[kp]));
-            GolLaunch g{};
-            geometry(e, kp, &g);
-            GolPersist pp{};
-            pp.epochs = (int32_t)std::min<int64_t>(count, 1 << 20);
-            pp.base_seq = e->seq;
-            pp.first_in = in;
-            pp.rot[0] = rot[0]; pp.rot[1] = rot[1]; pp.rot[2] = rot[2];
-            pp.chunk_rows = g.chunk_rows;
-            pp.items_per_domain = g.chunks * e->max_strips;
-            pp.ndoms = e->per_proc;
-            pp.wait_seq0 = multi(e) ? e->seq : 0;
-            const int64_t items = (int64_t)pp.ndoms * pp.items_per_domain;
-            if (pp.items_per_domain <= e->items_cap && e->persist_ctas[kp] > 0) {
-                const int ctas = (int)std::min<int64_t>(e->persist_ctas[kp], gol_div_up(items, 4));
-                pp.total_warps = ctas * GOL_STRIP_WARPS;
-                pp.work_counter = e->d_error + 1;
-                GOL_CUDA(cudaMemsetAsync(pp.work_counter, 0, sizeof(unsigned int), e->stream));
-                GOL_TRY(gol_launch_persistent(e->d_doms, pp, kp, ctas, e->stream));
-                ++e->launches;
-                e->seq += (uint32_t)pp.epochs;
-                e->prev_in = pp.epochs >= 2 ? rot[(pp.epochs - 2) % 3] : in;
-                in = rot[(pp.epochs - 1) % 3];
-                left -= (int64_t)pp.epochs * kp;
+    bool second = false;  // the next epoch completes a deep-halo pair
+    int k = 1;
+    while (left > 0) {
+        EpochMode mode = CLASSIC;
+        if (second) {
+            mode = PAIR_SECOND;
+            second = false;
+        } else {
+            k = per_gen_flags ? 1 : pick_depth(std::min<int64_t>(left, kcap));
+            if (e->deep_halo && !per_gen_flags && 2 * k <= G && left >= 2 * k) {
+                mode = PAIR_FIRST;
+                second = true;
             }
         }
-    }
-    while (left > 0) {
-        int k = 1;
-        if (!per_gen_flags) {
-            k = pick_depth(std::min<int64_t>(left, kcap), e);
-        }
         int out = -1;
-        for (int i = 0; i < GOL_NBUF; ++i)
-            if (i != in && (i != e->prev_in || !multi(e)) && i != keep && i != keep2) { out = i; break; }
-        if (out < 0)  // prev_in is only a hazard between ranks that run ahead; never when it is the last choice
-            for (int i = 0; i < GOL_NBUF; ++i)
-                if (i != in && i != keep && i != keep2) { out = i; break; }
+        GOL_TRY(pick_out(e, in, keep, keep2, &out));
         const bool last = left - k == 0;
         const bool f = per_gen_flags || (want_flags && last);
         uint32_t rs = 0;
@@ -448,15 +426,16 @@ int run_epochs(gol_engine *e, int64_t n, int keep, bool want_flags, bool per_gen
             rs = ++e->rec_seq;
             slot = (int)(rs % GOL_REC_SLOTS);
         }
-        GOL_TRY(launch_epoch(e, k, in, out, f, slot, rs));
+        GOL_TRY(launch_epoch(e, k, in, out, f, slot, rs, mode));
         if (f && per_gen_flags) {
             // in replay mode every generation is gathered (also keeps the record ring bounded)
             const ArenaLayout &A = e->arena_layout;
             GOL_TRY(gol_launch_gather(reinterpret_cast<unsigned long long *>(e->arena + A.rec_off), slot, e->ndom,
-                                      rs, e->d_results + (n - left), e->d_error, e->stream));
+                                      rs, e->d_results + (n - left), e->d_error, e->wait_timeout * 4, e->stream));
             ++e->launches;
         }
-        e->prev_in = in;
+        e->hist[1] = e->hist[0];
+        e->hist[0] = in;
         in = out;
         left -= k;
     }
@@ -470,7 +449,7 @@ int gather_last(gol_engine *e, int result_index)
     const ArenaLayout &A = e->arena_layout;
     GOL_TRY(gol_launch_gather(reinterpret_cast<unsigned long long *>(e->arena + A.rec_off),
                               (int)(rs % GOL_REC_SLOTS), e->ndom, rs, e->d_results + result_index, e->d_error,
-                              e->stream));
+                              e->wait_timeout * 4, e->stream));
     ++e->launches;
     return 0;
 }
@@ -566,7 +545,7 @@ int run_fast(gol_engine *e, gol_result *res)
         lp.in_idx = e->cur;
         lp.out_idx = e->cur;
         lp.seq = e->seq;  // no ghost traffic: sequence unchanged
-        lp.signal = 0;
+        lp.push = 0;
         const uint32_t rs = ++e->rec_seq;
         lp.rec_slot = (int)(rs % GOL_REC_SLOTS);
         lp.rec_seq = rs;
@@ -754,6 +733,10 @@ void gol_engine_destroy(gol_engine *e)
     if (!e) return;
     cudaSetDevice(e->cfg.device);
     if (e->stream) cudaStreamSynchronize(e->stream);
+    if (const char *tf = getenv("GOL_TRACE_FILE")) {
+        const std::string path = std::string(tf) + "." + std::to_string(e->rank);
+        gol_engine_trace_dump(e, path.c_str());
+    }
     for (int p = 0; p < (int)e->peer_arena.size(); ++p)
         if (p != e->rank && e->peer_arena[(size_t)p]) cudaIpcCloseMemHandle(e->peer_arena[(size_t)p]);
     if (e->arena) cudaFree(e->arena);
@@ -763,6 +746,9 @@ void gol_engine_destroy(gol_engine *e)
     if (e->h_results) cudaFreeHost(e->h_results);
     if (e->d_error) cudaFree(e->d_error);
     if (e->stage) cudaFree(e->stage);
+    if (e->d_trace) cudaFree(e->d_trace);
+    if (e->scratch_dense) cudaFree(e->scratch_dense);
+    if (e->d_count) cudaFree(e->d_count);
     if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
     if (e->ev_staged) cudaEventDestroy(e->ev_staged);
     if (e->ev_stage_free) cudaEventDestroy(e->ev_stage_free);
@@ -804,6 +790,7 @@ static int engine_create_impl(gol_engine *e)
     GOL_CUDA(cudaEventCreateWithFlags(&e->ev_slot[0], cudaEventDisableTiming));
     GOL_CUDA(cudaEventCreateWithFlags(&e->ev_slot[1], cudaEventDisableTiming));
 
+    GOL_CUDA(cudaMalloc(&e->d_count, 8));
     if (!e->fast) {
         const size_t bytes = (size_t)(gol_div_up(cfg.width, 64) * cfg.height) * sizeof(uint64_t);
         for (auto &d : e->dense) {
@@ -826,26 +813,43 @@ static int engine_create_impl(gol_engine *e)
         int64_t w, h;
         domain_extent(e, ld.gid, &ld.x0, &ld.y0, &w, &h);
         GOL_TRY(gol_layout_init(&ld.L, w, h));
-        GOL_TRY(gol_strip_geometry(ld.L.nw32, &ld.strips));
+        GOL_TRY(gol_strip_geometry(ld.L.nw32, 0, &ld.strips));
     }
     // launch geometry is uniform over all domains of the job (every process computes the same)
+    bool aligned = true;
     for (int g = 0; g < e->ndom; ++g) {
         int64_t x0, y0, w, h;
         domain_extent(e, g, &x0, &y0, &w, &h);
-        int s;
-        GOL_TRY(gol_strip_geometry(2 * (int)gol_div_up(w, 64), &s));
+        int s, sx;
+        GOL_TRY(gol_strip_geometry(2 * (int)gol_div_up(w, 64), 0, &s));
+        GOL_TRY(gol_strip_geometry(2 * (int)gol_div_up(w, 64), 2, &sx));
         e->max_strips = std::max(e->max_strips, s);
+        e->max_strips_ext = std::max(e->max_strips_ext, sx);
         e->max_h = std::max(e->max_h, h);
+        if (w % 64) aligned = false;
     }
-    e->items_cap = (int64_t)e->max_strips * gol_div_up(e->max_h, 8) + 64;
-    if (const char *v = getenv("GOL_PERSISTENT")) e->use_persistent = atoi(v) != 0;
     if (const char *v = getenv("GOL_AUTOTUNE")) e->autotune = atoi(v) != 0;
-    if (const char *v = getenv("GOL_PIPE")) {
-        int lv = 0, d = 0, occ = 0;
-        if (sscanf(v, "%dx%d", &lv, &d) == 2 && lv * d <= GOL_GHOST_ROWS && gol_pipe_ctas_per_sm(lv, d, &occ) == 0) {
-            e->pipe_lv = lv;
-            e->pipe_d = d;
-            if (e->cfg.k_max <= 0) e->kmax = lv * d;
+    // Deep-halo pairs: on by default between processes (GOL_DEEP_HALO=0 disables, =1 also enables them
+    // inside one process).  A pair's first epoch computes 64 ghost cells per side as whole words, so
+    // every domain width must be a multiple of 64, and two epochs must fit the 16-row ghost zone.
+    {
+        const char *v = getenv("GOL_DEEP_HALO");
+        const int want = v ? atoi(v) : -1;
+        e->deep_halo = aligned && 2 * e->kmax <= G && (want > 0 || (want < 0 && multi(e)));
+    }
+    if (const char *v = getenv("GOL_PDL")) e->pdl_multi = atoi(v) == 2;
+    {
+        // device-side flag waits: a rank that waits longer than this for a neighbour gives up with an error
+        const char *v = getenv("GOL_WAIT_TIMEOUT_MS");
+        const double ms = v ? atof(v) : 20000.0;
+        e->wait_timeout = (long long)(std::max(1.0, ms) * (double)prop.clockRate);  // clockRate is in kHz = cycles per ms
+    }
+    if (const char *v = getenv("GOL_TRACE")) {
+        e->trace_cap = std::max(0, atoi(v));
+        if (e->trace_cap) {
+            GOL_CUDA(cudaMalloc(&e->d_trace, sizeof(GolTrace) * (size_t)e->trace_cap));
+            std::vector<GolTrace> init((size_t)e->trace_cap, GolTrace{~0ull, 0ull, 0ull, 0ull});
+            GOL_CUDA(cudaMemcpy(e->d_trace, init.data(), sizeof(GolTrace) * init.size(), cudaMemcpyHostToDevice));
         }
     }
     if (getenv("GOL_VERBOSE")) e->cfg.flags |= GOL_FLAG_VERBOSE;
@@ -859,7 +863,7 @@ static int engine_create_impl(gol_engine *e)
     GOL_CUDA(cudaMalloc(&e->d_results, sizeof(unsigned long long) * (kMaxBatch + 2)));
     GOL_CUDA(cudaMemset(e->d_results, 0, sizeof(unsigned long long) * (kMaxBatch + 2)));
     GOL_CUDA(cudaMallocHost(&e->h_results, sizeof(unsigned long long) * (kMaxBatch + 2)));
-    GOL_CUDA(cudaMalloc(&e->d_error, 2 * sizeof(unsigned int)));   // [0] error word, [1] persistent work counter
+    GOL_CUDA(cudaMalloc(&e->d_error, 2 * sizeof(unsigned int)));
     GOL_CUDA(cudaMemset(e->d_error, 0, 2 * sizeof(unsigned int)));
     {
         size_t stage_bytes = 0;
@@ -868,6 +872,9 @@ static int engine_create_impl(gol_engine *e)
             stage_bytes += (size_t)ld.L.nq * (size_t)ld.L.height * 8;
         }
         GOL_CUDA(cudaMalloc(&e->stage, stage_bytes));
+        size_t scratch_bytes = 8;
+        for (const LocalDomain &ld : e->local) scratch_bytes = std::max(scratch_bytes, (size_t)ld.L.nq * (size_t)ld.L.height * 8);
+        GOL_CUDA(cudaMalloc(&e->scratch_dense, scratch_bytes));
         GOL_CUDA(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
         GOL_CUDA(cudaEventCreateWithFlags(&e->ev_staged, cudaEventDisableTiming));
         GOL_CUDA(cudaEventCreateWithFlags(&e->ev_stage_free, cudaEventDisableTiming));
@@ -1077,6 +1084,23 @@ int gol_engine_stage_packed(gol_engine *e, const uint64_t *host)
     return 0;
 }
 
+// One local domain of the next grid from the caller's own dense block [h][ceil(w/64)] (pinned memory
+// for an asynchronous copy): a rank keeps only its own blocks on the host.  Stage every local domain,
+// then commit.
+int gol_engine_stage_domain(gol_engine *e, int local_index, const uint64_t *host_dense)
+{
+    GOL_CUDA(cudaSetDevice(e->cfg.device));
+    if (!e->fast) GOL_FAIL("gol_engine_stage_domain: only for engines on the strip path");
+    if (local_index < 0 || local_index >= e->per_proc) GOL_FAIL("domain index %d out of range", local_index);
+    if (e->stage_busy) GOL_CUDA(cudaStreamWaitEvent(e->copy_stream, e->ev_stage_free, 0));  // last commit still reads it
+    const LocalDomain &ld = e->local[(size_t)local_index];
+    GOL_CUDA(cudaMemcpyAsync(e->stage + e->stage_off[(size_t)local_index], host_dense,
+                             (size_t)ld.L.nq * (size_t)ld.L.height * 8, cudaMemcpyHostToDevice, e->copy_stream));
+    GOL_CUDA(cudaEventRecord(e->ev_staged, e->copy_stream));
+    e->staged = true;
+    return 0;
+}
+
 int gol_engine_commit_staged(gol_engine *e)
 {
     GOL_CUDA(cudaSetDevice(e->cfg.device));
@@ -1131,18 +1155,16 @@ int gol_engine_randomize(gol_engine *e, uint64_t seed)
         return 0;
     }
     for (int i = 0; i < e->per_proc; ++i) {
+        // the engine-owned dense scratch is reused by every local domain: stream order keeps them apart
         const LocalDomain &ld = e->local[(size_t)i];
-        uint64_t *tmp = nullptr;
-        GOL_CUDA(cudaMalloc(&tmp, (size_t)ld.L.nq * (size_t)ld.L.height * 8));
-        int rc = gol_op_random_dense(tmp, ld.L.width, ld.L.height, ld.x0, ld.y0, seed, e->stream);
+        uint64_t *tmp = e->scratch_dense;
+        GOL_TRY(gol_op_random_dense(tmp, ld.L.width, ld.L.height, ld.x0, ld.y0, seed, e->stream));
         char *dst = e->arena + e->arena_layout.buf_off[(size_t)i * GOL_NBUF + e->cur];
-        if (!rc) rc = cudaMemsetAsync(dst, 0, (size_t)ld.L.buffer_words32 * 4, e->stream) != cudaSuccess;
-        if (!rc) rc = gol_launch_dense_to_padded(tmp, ld.L.nq, 0, reinterpret_cast<uint32_t *>(dst), ld.L, e->stream);
+        GOL_CUDA(cudaMemsetAsync(dst, 0, (size_t)ld.L.buffer_words32 * 4, e->stream));
+        GOL_TRY(gol_launch_dense_to_padded(tmp, ld.L.nq, 0, reinterpret_cast<uint32_t *>(dst), ld.L, e->stream));
         e->launches += 2;
-        cudaStreamSynchronize(e->stream);
-        cudaFree(tmp);
-        if (rc) return 1;
     }
+    GOL_CUDA(cudaStreamSynchronize(e->stream));
     return 0;
 }
 
@@ -1164,6 +1186,58 @@ int gol_engine_download_packed(gol_engine *e, uint64_t *host)
                                    (size_t)ld.L.nq * 8, (size_t)ld.L.height, cudaMemcpyDeviceToHost, e->stream));
     }
     GOL_CUDA(cudaStreamSynchronize(e->stream));
+    return 0;
+}
+
+// One local domain of the current grid into the caller's dense block [h][ceil(w/64)]: a kernel
+// gathers the padded rows into the engine's dense scratch, one linear copy brings them to the host.
+int gol_engine_download_domain(gol_engine *e, int local_index, uint64_t *host_dense)
+{
+    GOL_CUDA(cudaSetDevice(e->cfg.device));
+    if (!e->fast) {
+        if (local_index != 0) GOL_FAIL("domain index %d out of range", local_index);
+        GOL_CUDA(cudaMemcpyAsync(host_dense, e->dense[e->cur], (size_t)(gol_div_up(e->cfg.width, 64) * e->cfg.height) * 8,
+                                 cudaMemcpyDeviceToHost, e->stream));
+        GOL_CUDA(cudaStreamSynchronize(e->stream));
+        return 0;
+    }
+    if (local_index < 0 || local_index >= e->per_proc) GOL_FAIL("domain index %d out of range", local_index);
+    const LocalDomain &ld = e->local[(size_t)local_index];
+    const char *src = e->arena + e->arena_layout.buf_off[(size_t)local_index * GOL_NBUF + e->cur];
+    GOL_TRY(gol_launch_padded_to_dense(reinterpret_cast<const uint32_t *>(src), ld.L, e->scratch_dense, ld.L.nq, 0, 0, e->stream));
+    ++e->launches;
+    GOL_CUDA(cudaMemcpyAsync(host_dense, e->scratch_dense, (size_t)ld.L.nq * (size_t)ld.L.height * 8, cudaMemcpyDeviceToHost,
+                             e->stream));
+    GOL_CUDA(cudaStreamSynchronize(e->stream));
+    return 0;
+}
+
+// Checksum of the local part of the current grid (see hash_padded_kernel): add the values of all
+// processes (mod 2^64) to get a number that identifies the global grid whatever the decomposition.
+int gol_engine_hash(gol_engine *e, uint64_t *hash)
+{
+    GOL_CUDA(cudaSetDevice(e->cfg.device));
+    GOL_CUDA(cudaMemsetAsync(e->d_count, 0, 8, e->stream));
+    if (!e->fast) {
+        gol_layout L;
+        GOL_TRY(gol_layout_init(&L, e->cfg.width, e->cfg.height));
+        // dense buffer = a padded layout without ghosts: same kernel, shifted so that its offsets vanish
+        L.pitch32 = L.nw32;
+        GOL_TRY(gol_launch_hash_padded(reinterpret_cast<const uint32_t *>(e->dense[e->cur]) - ((int64_t)G * L.pitch32 + GOL_GHOST_WORDS32),
+                                       L, 0, 0, e->d_count, e->stream));
+        ++e->launches;
+    } else {
+        for (int i = 0; i < e->per_proc; ++i) {
+            const LocalDomain &ld = e->local[(size_t)i];
+            const char *src = e->arena + e->arena_layout.buf_off[(size_t)i * GOL_NBUF + e->cur];
+            GOL_TRY(gol_launch_hash_padded(reinterpret_cast<const uint32_t *>(src), ld.L, ld.x0 / 64, ld.y0, e->d_count, e->stream));
+            ++e->launches;
+        }
+    }
+    unsigned long long c = 0;
+    GOL_CUDA(cudaMemcpyAsync(&c, e->d_count, 8, cudaMemcpyDeviceToHost, e->stream));
+    GOL_CUDA(cudaStreamSynchronize(e->stream));
+    *hash = c;
     return 0;
 }
 
@@ -1362,7 +1436,8 @@ int gol_engine_prepare(gol_engine *e)
         lp.out_idx = e->cur;
         lp.wait_seq = 0;
         lp.seq = ++e->seq;
-        lp.signal = multi(e) ? 1 : 0;
+        lp.push = multi(e) ? 3 : 1;
+        lp.push_rows = G;
         lp.rec_slot = -1;
         GOL_TRY(gol_launch_halo(e->d_doms, e->per_proc, lp, e->stream));
         ++e->launches;
@@ -1418,37 +1493,61 @@ int gol_engine_sync(gol_engine *e)
 }
 
 int64_t gol_engine_launch_count(const gol_engine *e) { return e->launches; }
+
+int gol_engine_chunk_rows(const gol_engine *e)
+{
+    if (!e->fast) return 0;
+    GolLaunch lp{};
+    geometry(e, e->kmax, &lp);
+    return lp.chunk_rows;
+}
+
+int gol_engine_uses_deep_halo(const gol_engine *e) { return e->deep_halo ? 1 : 0; }
+
+// Writes the per-launch timeline (GOL_TRACE=<n> at creation) as text: one line per strip-kernel
+// launch with its depth, epoch mode (0 classic, 1 pair-first, 2 pair-second), flag bit, duration
+// (first CTA start to last CTA end), gap to the previous launch's end and flag spin cycles.
+int gol_engine_trace_dump(gol_engine *e, const char *path)
+{
+    if (!e->d_trace || !e->trace_n) return 0;
+    GOL_CUDA(cudaSetDevice(e->cfg.device));
+    GOL_CUDA(cudaStreamSynchronize(e->stream));
+    std::vector<GolTrace> t((size_t)e->trace_n);
+    GOL_CUDA(cudaMemcpy(t.data(), e->d_trace, sizeof(GolTrace) * t.size(), cudaMemcpyDeviceToHost));
+    FILE *f = fopen(path, "w");
+    if (!f) GOL_FAIL("fopen: %s: %s", path, strerror(errno));
+    fprintf(f, "# launch k mode flags start_ns dur_ns gap_ns spin_sum_cycles spin_max_cycles\n");
+    for (size_t i = 0; i < t.size(); ++i) {
+        const int m = e->trace_meta[i];
+        const long long gap = i ? (long long)t[i].t0_min - (long long)t[i - 1].t1_max : 0;
+        fprintf(f, "%zu %d %d %d %llu %lld %lld %llu %llu\n", i, m & 255, (m >> 8) & 255, (m >> 16) & 1,
+                t[i].t0_min - t[0].t0_min, (long long)(t[i].t1_max - t[i].t0_min), gap, t[i].spin_sum, t[i].spin_max);
+    }
+    fclose(f);
+    return 0;
+}
 double gol_engine_last_ms(const gol_engine *e) { return e->last_ms; }
 
 int gol_engine_population(gol_engine *e, uint64_t *count)
 {
     GOL_CUDA(cudaSetDevice(e->cfg.device));
-    unsigned long long *d_count = nullptr;
-    GOL_CUDA(cudaMalloc(&d_count, 8));
-    cudaMemsetAsync(d_count, 0, 8, e->stream);
-    int rc = 0;
+    unsigned long long *d_count = e->d_count;   // engine-owned: no allocation on this path
+    GOL_CUDA(cudaMemsetAsync(d_count, 0, 8, e->stream));
     if (!e->fast) {
-        rc = gol_op_popcount_dense(e->dense[e->cur], e->cfg.width, e->cfg.height, d_count, e->stream);
+        GOL_TRY(gol_op_popcount_dense(e->dense[e->cur], e->cfg.width, e->cfg.height, d_count, e->stream));
         ++e->launches;
     } else {
-        for (int i = 0; i < e->per_proc && !rc; ++i) {
-            const LocalDomain &ld = e->local[(size_t)i];
-            uint64_t *tmp = nullptr;
-            if (cudaMalloc(&tmp, (size_t)ld.L.nq * (size_t)ld.L.height * 8) != cudaSuccess) { gol_set_error("out of memory"); rc = 1; break; }
+        for (int i = 0; i < e->per_proc; ++i) {
             const char *src = e->arena + e->arena_layout.buf_off[(size_t)i * GOL_NBUF + e->cur];
-            rc = gol_launch_padded_to_dense(reinterpret_cast<const uint32_t *>(src), ld.L, tmp, ld.L.nq, 0, 0, e->stream);
-            if (!rc) rc = gol_op_popcount_dense(tmp, ld.L.width, ld.L.height, d_count, e->stream);
-            e->launches += 2;
-            cudaStreamSynchronize(e->stream);
-            cudaFree(tmp);
+            GOL_TRY(gol_launch_popcount_padded(reinterpret_cast<const uint32_t *>(src), e->local[(size_t)i].L, d_count, e->stream));
+            ++e->launches;
         }
     }
     unsigned long long c = 0;
-    if (!rc && cudaMemcpyAsync(&c, d_count, 8, cudaMemcpyDeviceToHost, e->stream) != cudaSuccess) rc = 1;
-    cudaStreamSynchronize(e->stream);
-    cudaFree(d_count);
+    GOL_CUDA(cudaMemcpyAsync(&c, d_count, 8, cudaMemcpyDeviceToHost, e->stream));
+    GOL_CUDA(cudaStreamSynchronize(e->stream));
     *count = c;
-    return rc;
+    return 0;
 }
 
 int gol_engine_domain_buffer(gol_engine *e, int i, void **d_ptr, gol_layout *layout)

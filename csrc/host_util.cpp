@@ -310,6 +310,21 @@ extern "C" int gol_random_text_file(const char *path, int64_t W, int64_t H, uint
     return 0;
 }
 
+extern "C" int gol_hash_packed(const uint64_t *packed, int64_t W, int64_t H, uint64_t *hash)
+{
+    if (W < 1 || H < 1 || !packed || !hash) GOL_FAIL("gol_hash_packed: bad argument");
+    const int64_t nq = gol_div_up(W, 64);
+    std::atomic<uint64_t> total{0};
+    parallel_rows(H, 0, [&](int64_t y0, int64_t y1) {
+        uint64_t c = 0;
+        for (int64_t y = y0; y < y1; ++y)
+            for (int64_t q = 0; q < nq; ++q) c += gol_hash64(packed[y * nq + q], (uint64_t)q, (uint64_t)y);
+        total += c;
+    });
+    *hash = total.load();
+    return 0;
+}
+
 extern "C" int gol_write_pbm(const char *path, const uint64_t *packed, int64_t W, int64_t H)
 {
     if (W < 1 || H < 1) GOL_FAIL("grid dimensions must be positive");

@@ -1,9 +1,9 @@
 // gol_engine_population_static: the live-cell count of an engine's grid for callers that must not
 // allocate device memory.
 //
-// gol_engine_population() stages every local domain into a dense temporary and keeps its counter
-// in device memory, both obtained with cudaMalloc on every call.  Some hosts of this library
-// cannot do that: a process whose device memory has been handed over wholesale to another
+// gol_engine_population() keeps its counter in device memory that the engine obtains with
+// cudaMalloc (the generic dense path also stages through cudaMalloc'ed memory).  Some hosts of this
+// library cannot allocate: a process whose device memory has been handed over wholesale to another
 // allocator (a framework memory pool that owns the whole GPU, so a raw cudaMalloc fails or fights
 // the pool), or a loop with a latency budget, where the implicit device synchronisation of
 // cudaMalloc / cudaFree stalls every stream of the process.  This variant runs the same two
@@ -24,6 +24,13 @@ constexpr size_t kCounterBytes = 256;  // first 256 bytes: the 64-bit counter (k
 
 // In host code this name is only a handle for the runtime's symbol table, never a device address.
 static __device__ __align__(256) unsigned char g_static_scratch[kCounterBytes + GOL_STATIC_SCRATCH_BYTES];
+
+// Puts the caller's current device back when the entry point returns (on every path).
+struct DeviceRestore {
+    int prev = -1;
+    DeviceRestore() { if (cudaGetDevice(&prev) != cudaSuccess) prev = -1; }
+    ~DeviceRestore() { if (prev >= 0) cudaSetDevice(prev); }
+};
 
 std::mutex g_mutex;
 unsigned char *g_device_ptr[kMaxDevices];  // resolved once per device
@@ -56,6 +63,7 @@ extern "C" int gol_engine_population_static(gol_engine *e, uint64_t *count)
     GOL_TRY(gol_engine_domain_buffer(e, 0, &d_first, &L0));
     cudaPointerAttributes attr;
     GOL_CUDA(cudaPointerGetAttributes(&attr, d_first));
+    DeviceRestore restore;  // the grid's device is made current below; the caller's comes back on return
     GOL_CUDA(cudaSetDevice(attr.device));
 
     // refuse before touching anything if a domain does not fit the fixed staging area

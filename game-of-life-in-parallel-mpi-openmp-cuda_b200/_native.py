@@ -111,6 +111,14 @@ def _proto(lib):
         "gol_engine_run": (i32, [vp, C.POINTER(Result)]),
         "gol_engine_sync": (i32, [vp]),
         "gol_engine_launch_count": (i64, [vp]),
+        "gol_engine_chunk_rows": (i32, [vp]),
+        "gol_engine_stage_domain": (i32, [vp, i32, vp]),
+        "gol_engine_download_domain": (i32, [vp, i32, vp]),
+        "gol_engine_hash": (i32, [vp, p64]),
+        "gol_hash_packed": (i32, [vp, i64, i64, p64]),
+        "gol_engine_uses_deep_halo": (i32, [vp]),
+        "gol_engine_trace_dump": (i32, [vp, C.c_char_p]),
+        "gol_engine_population_static": (i32, [vp, p64]),
         "gol_engine_population": (i32, [vp, p64]),
         "gol_engine_domain_buffer": (i32, [vp, i32, C.POINTER(vp), C.POINTER(Layout)]),
         "gol_engine_last_ms": (C.c_double, [vp]),

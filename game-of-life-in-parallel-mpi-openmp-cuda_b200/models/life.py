@@ -143,6 +143,20 @@ class GameOfLife:
         return bool(self._lib.gol_engine_uses_fast_path(self._h))
 
     @property
+    def uses_deep_halo(self) -> bool:
+        """Epochs run as pairs with one 16-deep halo exchange per pair (default between processes)."""
+        return bool(self._lib.gol_engine_uses_deep_halo(self._h))
+
+    @property
+    def chunk_rows(self) -> int:
+        """Height of the interior chunks at the engine's temporal depth (autotuned in prepare())."""
+        return int(self._lib.gol_engine_chunk_rows(self._h))
+
+    def trace_dump(self, path: str) -> None:
+        """Per-launch device timeline of an engine created with GOL_TRACE=<n> in the environment."""
+        N.check(self._lib.gol_engine_trace_dump(self._h, str(path).encode()), "trace_dump")
+
+    @property
     def num_domains(self) -> int:
         return int(self._lib.gol_engine_num_domains(self._h))
 

@@ -206,6 +206,12 @@ int gol_engine_load_packed(gol_engine *e, const uint64_t *host_packed); /* globa
  * grid into the current one.  Between the two calls the engine may be running the previous grid. */
 int gol_engine_stage_packed(gol_engine *e, const uint64_t *host_packed);
 int gol_engine_commit_staged(gol_engine *e);
+/* Per-domain variants for callers that keep only their own blocks on the host: local domain
+ * `local_index` as packed dense rows [h][ceil(w/64)].  stage_domain is asynchronous like
+ * stage_packed (stage every local domain, then commit); download_domain returns when the data is
+ * in host memory. */
+int gol_engine_stage_domain(gol_engine *e, int local_index, const uint64_t *host_dense);
+int gol_engine_download_domain(gol_engine *e, int local_index, uint64_t *host_dense);
 int gol_engine_load_packed_device(gol_engine *e, const uint64_t *d_packed, int64_t x0,
                                   int64_t y0, int64_t w, int64_t h);    /* one local block */
 int gol_engine_randomize(gol_engine *e, uint64_t seed);
@@ -232,7 +238,21 @@ int gol_engine_sync(gol_engine *e);
 
 /* Kernel launches issued by this engine since creation (for bench accounting). */
 int64_t gol_engine_launch_count(const gol_engine *e);
+/* Tuning facts for reports: height of the interior chunks the strip kernel uses at the engine's
+ * temporal depth (after gol_engine_prepare: the autotuned value); whether epochs run as deep-halo
+ * pairs (one halo exchange per two epochs). */
+int gol_engine_chunk_rows(const gol_engine *e);
+int gol_engine_uses_deep_halo(const gol_engine *e);
+/* Per-launch device timeline (engines created with GOL_TRACE=<max launches> in the environment):
+ * text file, one line per generation-kernel launch. */
+int gol_engine_trace_dump(gol_engine *e, const char *path);
 /* Local population / flags of the current buffer. */
+/* gol_engine_hash: position-dependent 64-bit checksum of the local domains (sum over words of
+ * hash(value, global word x, global row y), mod 2^64).  The sum over all processes identifies the
+ * global grid independently of the decomposition; gol_hash_packed is the same number computed
+ * on the host from a packed dense grid. */
+int gol_engine_hash(gol_engine *e, uint64_t *hash);
+int gol_hash_packed(const uint64_t *packed, int64_t width, int64_t height, uint64_t *hash);
 int gol_engine_population(gol_engine *e, uint64_t *count);
 
 /* Same result as gol_engine_population, for callers that may not allocate device memory: a

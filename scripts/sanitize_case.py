@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Small end-to-end case for `compute-sanitizer --tool memcheck|initcheck`: every kernel of the
 library on sizes that exercise the ragged right edge, multi-strip rows, multi-domain pushes, the
-flag/record protocol, early-exit replay, the persistent kernel and the text kernels."""
+flag/record protocol, early-exit replay, deep-halo epoch pairs and the text kernels."""
 import os
 import sys
 import tempfile
@@ -35,14 +35,16 @@ tmp = os.path.join(tempfile.gettempdir(), "san.txt")
 life.save(tmp)
 life.load_file(tmp)
 life.close()
-# persistent kernel
-os.environ["GOL_PERSISTENT"] = "1"
-life = gol_b200.GameOfLife(1100, 300, device=0, k_max=4)
-start = cpu.random_grid(1100, 300, 5)
-life.load_packed(start)
-life.step(24)
-assert np.array_equal(life.packed_numpy(), cpu.step(start, 1100, 24))
-life.close()
+# deep-halo epoch pairs inside one process
+os.environ["GOL_DEEP_HALO"] = "1"
+for grid in [(1, 1), (2, 2)]:
+    life = gol_b200.GameOfLife(1152, 300, device=0, grid=grid)
+    start = cpu.random_grid(1152, 300, 5)
+    life.load_packed(start)
+    life.step(48)
+    assert np.array_equal(life.packed_numpy(), cpu.step(start, 1152, 48))
+    life.close()
+del os.environ["GOL_DEEP_HALO"]
 # dense ops
 g = dense.random_grid(130, 33, 3, device="cuda:0")
 f = torch.zeros(2, dtype=torch.int32, device="cuda:0")

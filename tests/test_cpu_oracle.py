@@ -146,14 +146,14 @@ def test_topology():
 
 
 def test_kernel_rule_circuit_truth_table():
-    """The LOP3 circuit of life_rule() in csrc/life_kernels.cu (read from the source) equals B3/S23
+    """The LOP3 circuit of life_rule() in csrc/life_march.cuh (read from the source) equals B3/S23
     on all 4*4*4*2 combinations of the three row sums and the centre bit (reference rule: S:60-101)."""
     import itertools
     import os
     import re
-    src = open(os.path.join(os.path.dirname(__file__), "..", "csrc", "life_kernels.cu")).read()
-    body = src[src.index("#else", src.index("life_rule(uint32_t a0")):]
-    body = body[:body.index("#endif")]
+    src = open(os.path.join(os.path.dirname(__file__), "..", "csrc", "life_march.cuh")).read()
+    body = src[src.index("life_rule(uint32_t a0"):]
+    body = body[:body.index("\n}\n")]
     stmts = re.findall(r"(\w+) = (xor3|maj3|lop3<0x([0-9A-Fa-f]+)>)\((\w+), (\w+), (\w+)\);", body)
     ret = re.search(r"return lop3<0x([0-9A-Fa-f]+)>\((\w+), (\w+), (\w+)\);", body)
     assert len(stmts) == 5 and ret, "life_rule is expected to be 6 LOP3"

@@ -193,14 +193,13 @@ def test_cli_matches_unmodified_reference(cuda_device, ref_serial, tmp_path):
     assert p.stdout == "Finished\n"
 
 
-def test_end_to_end_case_with_persistent_kernel(cuda_device):
-    # scripts/sanitize_case.py walks every kernel of the library, including the opt-in persistent
-    # (dataflow) kernel, and checks each against the CPU oracle; it is also the case meant for
-    # compute-sanitizer (closed on this pool, so it is run plain here)
+def test_end_to_end_case(cuda_device):
+    # scripts/sanitize_case.py walks every kernel of the library (deep-halo epoch pairs included) and
+    # checks each against the CPU oracle; it is also the case meant for compute-sanitizer (closed on
+    # this pool, so it is run plain here)
     import sys
-    env = dict(os.environ, GOL_PERSISTENT="1")
     p = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "sanitize_case.py")], capture_output=True,
-                       text=True, timeout=300, env=env)
+                       text=True, timeout=300)
     assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
     assert "sanitize case ok" in p.stdout
 
@@ -264,16 +263,20 @@ def test_cli_one_process_per_gpu(cuda_device, tmp_path):
     assert (tmp_path / "cuda_output.out").read_bytes() == want
 
 
-@pytest.mark.parametrize("cfg", ["4x2", "2x4", "4x4"])
-def test_warp_pipelined_kernel(cuda_device, cfg):
-    # opt-in kernel variant (GOL_PIPE=LVxD): D warps of a CTA form a pipeline of LV generations each,
-    # rows travel through shared-memory FIFOs; must be bit-identical to the oracle like the default
-    import sys
-    env = dict(os.environ, GOL_PIPE=cfg)
-    p = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "pipe_check.py"), "--no-timing"],
-                       capture_output=True, text=True, timeout=300, env=env)
-    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
-    assert "pipe check ok" in p.stdout
+@pytest.mark.parametrize("grid", [(1, 1), (1, 2), (2, 1), (2, 2), (2, 4), (8, 1), (3, 3)])
+def test_deep_halo_pairs_emulated(cuda_device, monkeypatch, grid):
+    # GOL_DEEP_HALO=1 switches the pair schedule on inside one process: the first epoch of a pair also
+    # computes the ghost rows / ghost words next to every domain, the second one needs no exchange
+    monkeypatch.setenv("GOL_DEEP_HALO", "1")
+    life = make(2240, 384, grid=grid)
+    assert life.uses_deep_halo
+    life.close()
+    check_steps(2240, 384, [16, 1, 32, 7, 48, 100], grid=grid)
+    check_steps(1536, 210, [16, 33], grid=grid, seed=3, k_max=4)
+    check_steps(1536, 100, [64], grid=(1, 1), seed=4)       # single-chunk domains (shorter than three edge chunks)
+    from gol_b200.utils import patterns
+    cells = patterns.grid_with(1024, 128, ("tromino", 510, 62), ("diag3", 700, 100))
+    run_both(cells, gen_limit=200, grid=grid if 128 // grid[0] >= 16 else (1, 1))
 
 
 def test_staged_upload(cuda_device):
