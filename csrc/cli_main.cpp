@@ -88,7 +88,7 @@ void usage()
             "  --gen-limit N            GEN_LIMIT (default 1000)\n"
             "  --similarity-frequency F SIMILARITY_FREQUENCY (default 3), --no-similarity disables\n"
             "  --gpus N                 one process per GPU (default 1)\n"
-            "  --grid RxC               domain decomposition (default: near-square for --gpus/--ranks)\n"
+            "  --grid RxC               domain decomposition (default: N x 1 slabs up to 16 domains)\n"
             "  --ranks X                number of domains (like mpiexec -n X); may exceed --gpus\n"
             "  --k K --batch B          temporal depth per launch / generations per flag check\n"
             "  --start-generation G     resume: the input file is generation G of an earlier run\n"
@@ -100,8 +100,16 @@ void usage()
             "  --no-write --stats\n");
 }
 
-void auto_grid(int n, int *r, int *c)
+// Default decomposition: horizontal slabs (n x 1) for up to 16 domains that leave every slab at least
+// 48 rows - full-width rows, so only whole ghost rows travel between neighbours (measured faster than
+// column splits, see profiles/README.md); otherwise near-square.
+void auto_grid(int n, long long height, int *r, int *c)
 {
+    if (n <= 16 && height / n >= 48) {
+        *r = n;
+        *c = 1;
+        return;
+    }
     int best = 1;
     for (int i = 1; i * i <= n; ++i)
         if (n % i == 0) best = i;
@@ -296,7 +304,7 @@ int main(int argc, char **argv)
         if (opt.gpus < 1) opt.gpus = 1;
         if (opt.gpus > 64) opt.gpus = 64;
         int ndom = opt.grid_r > 0 && opt.grid_c > 0 ? opt.grid_r * opt.grid_c : (opt.ranks > 0 ? opt.ranks : opt.gpus);
-        if (opt.grid_r <= 0 || opt.grid_c <= 0) auto_grid(ndom, &opt.grid_r, &opt.grid_c);
+        if (opt.grid_r <= 0 || opt.grid_c <= 0) auto_grid(ndom, opt.height, &opt.grid_r, &opt.grid_c);
         if (ndom % opt.gpus) {
             fprintf(stderr, "%d domains cannot be dealt evenly to %d processes\n", ndom, opt.gpus);
             return EXIT_FAILURE;

@@ -92,7 +92,7 @@ struct gol_engine {
     int tuned_rows[17] = {0};       // measured best chunk height per temporal depth (0 = not tuned yet)
     bool autotune = true;           // GOL_AUTOTUNE=0 disables the one-off geometry timing
     bool deep_halo = false;         // epochs run as pairs with one 16-deep halo exchange per pair (see run_epochs)
-    bool pdl_multi = false;         // GOL_PDL=2: programmatic dependent launch also between processes
+    int pdl_mode = 2;               // GOL_PDL: 0 no programmatic dependent launch, 1 single-process engines only, 2 always
     long long wait_timeout = 0;     // device-side flag waits give up after this many clock cycles
     // GOL_TRACE=<n>: per-launch timeline records (first CTA start, last CTA end, flag spin cycles)
     GolTrace *d_trace = nullptr;
@@ -227,6 +227,7 @@ int upload_domains(gol_engine *e)
 }
 
 bool multi(const gol_engine *e) { return e->P > 1; }
+int uses_pdl(const gol_engine *e) { return e->pdl_mode >= 2 || (e->pdl_mode == 1 && !multi(e)) ? 1 : 0; }
 
 // Launch geometry for temporal depth k.  Every domain is cut into a first and a last chunk of
 // GOL_EDGE_ROWS rows (the rows that are exchanged with the north / south neighbours; short, so that
@@ -298,7 +299,7 @@ int launch_epoch(gol_engine *e, int k, int in, int out, bool flags, int rec_slot
     lp.push_rows = G;
     // waiting items go last (the neighbours' flags have a whole epoch to arrive), pushing items first
     lp.border_last = mode == PAIR_FIRST ? 1 : 0;
-    lp.pdl = (!multi(e) || e->pdl_multi) ? 1 : 0;
+    lp.pdl = uses_pdl(e);
     lp.rec_slot = flags ? rec_slot : -1;
     lp.rec_seq = rec_seq;
     lp.trace = next_trace(e, k, mode, flags);
@@ -346,7 +347,7 @@ int autotune_geometry(gol_engine *e, int k, int in, int scratch)
         lp.wait_seq = 0;
         lp.push = 0;                 // no pushes, no flags
         lp.push_rows = G;
-        lp.pdl = (!multi(e) || e->pdl_multi) ? 1 : 0;   // same launch mode as the real epochs
+        lp.pdl = uses_pdl(e);        // same launch mode as the real epochs
         lp.rec_slot = -1;
         GOL_TRY(gol_launch_strip(e->d_doms, e->per_proc, lp, k, 0, e->stream));
         GOL_CUDA(cudaEventRecord(e->ev_tune[0], e->stream));
@@ -837,7 +838,7 @@ static int engine_create_impl(gol_engine *e)
         const int want = v ? atoi(v) : -1;
         e->deep_halo = aligned && 2 * e->kmax <= G && (want > 0 || (want < 0 && multi(e)));
     }
-    if (const char *v = getenv("GOL_PDL")) e->pdl_multi = atoi(v) == 2;
+    if (const char *v = getenv("GOL_PDL")) e->pdl_mode = atoi(v);
     {
         // device-side flag waits: a rank that waits longer than this for a neighbour gives up with an error
         const char *v = getenv("GOL_WAIT_TIMEOUT_MS");

@@ -216,7 +216,42 @@ class GameOfLife:
         N.check(self._lib.gol_engine_stage_packed(self._h, C.c_void_p(ptr)), "stage_packed")
         return self
 
-    def commit_staged(self, stage_next=None) -> "GameOfLife":
+    def local_block_shape(self, local_index: int = 0) -> tuple[int, int]:
+        """(rows, 64-bit words per row) of a local domain's packed dense block."""
+        _, _, w, h = self.domain_extent(self.local_domains[local_index])
+        return h, words_per_row(w)
+
+    def stage_local(self, blocks) -> "GameOfLife":
+        """Like stage_packed, but from the rank's OWN blocks: one pinned int64 CPU tensor
+        [h, ceil(w/64)] per local domain (local_block_shape), so a rank never holds the global grid."""
+        if len(blocks) != len(self.local_domains):
+            raise ValueError("one block per local domain")
+        for i, b in enumerate(blocks):
+            if tuple(b.shape) != self.local_block_shape(i) or not b.is_contiguous():
+                raise ValueError(f"block {i} must be contiguous with shape {self.local_block_shape(i)}")
+            N.check(self._lib.gol_engine_stage_domain(self._h, i, C.c_void_p(b.data_ptr())), "stage_domain")
+        self._staged_keepalive = blocks
+        return self
+
+    def download_local(self, blocks) -> "GameOfLife":
+        """Current grid of every local domain into the caller's blocks (pinned int64 CPU tensors,
+        local_block_shape); returns when the data is in host memory."""
+        if len(blocks) != len(self.local_domains):
+            raise ValueError("one block per local domain")
+        for i, b in enumerate(blocks):
+            if tuple(b.shape) != self.local_block_shape(i) or not b.is_contiguous():
+                raise ValueError(f"block {i} must be contiguous with shape {self.local_block_shape(i)}")
+            N.check(self._lib.gol_engine_download_domain(self._h, i, C.c_void_p(b.data_ptr())), "download_domain")
+        return self
+
+    def local_hash(self) -> int:
+        """Checksum of the local domains; the sum over all ranks (mod 2**64) identifies the global
+        grid independently of the decomposition (gol_engine_hash)."""
+        c = C.c_uint64()
+        N.check(self._lib.gol_engine_hash(self._h, C.byref(c)), "hash")
+        return int(c.value)
+
+    def commit_staged(self, stage_next=None, stage_next_local=None) -> "GameOfLife":
         """Make the staged grid the current one (then run()/step() as after load_packed).
         `stage_next`: start uploading the grid after this one right away (same as calling
         stage_packed() next, but issued before the ranks synchronise, so the host time of the
@@ -224,6 +259,8 @@ class GameOfLife:
         N.check(self._lib.gol_engine_commit_staged(self._h), "commit_staged")
         if stage_next is not None:
             self.stage_packed(stage_next)
+        if stage_next_local is not None:
+            self.stage_local(stage_next_local)
         self._after_load()
         return self
 

@@ -109,3 +109,12 @@ def random_text_file(path: str, width: int, height: int, seed: int = 1) -> None:
 def write_pbm(path: str, packed: np.ndarray, width: int) -> None:
     packed = np.ascontiguousarray(packed, dtype=np.uint64)
     N.check(N.lib().gol_write_pbm(path.encode(), _ptr(packed), width, packed.shape[0]), "gol_write_pbm")
+
+
+def grid_hash(packed: np.ndarray, width: int) -> int:
+    """Position-dependent 64-bit checksum of a packed grid (gol_hash_packed); equals the sum of
+    GameOfLife.local_hash() over all ranks for the same grid."""
+    packed = np.ascontiguousarray(packed, dtype=np.uint64)
+    c = C.c_uint64()
+    N.check(N.lib().gol_hash_packed(packed.ctypes.data_as(C.c_void_p), width, packed.shape[0], C.byref(c)), "hash_packed")
+    return int(c.value)

@@ -130,8 +130,10 @@ def test_pbm_dump(tmp_path):
 
 
 def test_topology():
-    from gol_b200.parallel import Topology, auto_grid, OPPOSITE
-    assert auto_grid(8) == (2, 4) and auto_grid(4) == (2, 2) and auto_grid(2) == (1, 2) and auto_grid(1) == (1, 1)
+    from gol_b200.parallel import Topology, auto_grid, near_square_grid, OPPOSITE
+    g = near_square_grid
+    assert g(8) == (2, 4) and g(4) == (2, 2) and g(2) == (1, 2) and g(1) == (1, 1)
+    assert auto_grid(8) == (8, 1) and auto_grid(2) == (2, 1) and auto_grid(1) == (1, 1) and auto_grid(64) == (8, 8)
     t = Topology(65536, 65536, 2, 4)
     assert t.neighbors(0) == [4, 4, 3, 1, 7, 5, 7, 5]
     for g in range(t.size):

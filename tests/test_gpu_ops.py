@@ -106,4 +106,8 @@ def test_bench_contract(cuda_device):
     assert d["n_gpus"] == 1 and d["steps"] == 2 and d["warmup"] == 3 and d["higher_is_better"] is True
     assert d["value"] > 0 and d["e2e"]["value"] > 0 and d["e2e"]["value"] < d["value"] * 1.001
     assert d["e2e"]["h2d_bytes_per_step"] == 2048 * 2048 // 8 and d["gpu_launches"] > 0
-    assert d["config"]["generations_reported"] == 200 and d["config"]["fast_path"] is True
+    assert d["details"]["generations_reported"] == 200 and d["details"]["fast_path"] is True
+    assert d["e2e"]["d2h_bytes_per_step"] >= 2048 * 2048 // 8          # the final grid comes back every step
+    assert d["verify"]["hash_equal"] and d["verify"]["population_equal"] and d["verify"]["downloaded_grid_population_equal"]
+    assert d["cli_wall"]["generations"] == 200 and d["cli_wall"]["ms"] > 0
+    assert d["details"]["chunk_rows"] > 0 and len(d["details"]["grid_hash"]) == 16
