@@ -200,9 +200,12 @@ def bench_ours(args):
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    cdev = dev
     if world > 1:
+        import datetime
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        # a rank that dies must not leave the others waiting for ten minutes
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
     R, C = (int(v) for v in args.grid.split("x")) if args.grid else auto_grid(world)
     W, H = C * args.size, R * args.size
     freq = 0 if args.no_similarity else FREQ
@@ -268,11 +271,11 @@ def bench_ours(args):
 
     # identity of the final grid: decomposition-independent checksum + population, summed over the ranks
     lh = life.local_hash()
-    ident = torch.tensor([lh - (1 << 64) if lh >= (1 << 63) else lh, life.population()], dtype=torch.int64, device=dev)
+    ident = torch.tensor([lh - (1 << 64) if lh >= (1 << 63) else lh, life.population()], dtype=torch.int64, device=cdev)
     # the downloaded blocks are that grid: their host-side checksum must agree with the device's
     host_pop = int(sum(int(np.unpackbits(b.numpy().view(np.uint8)).sum()) for b in host_out))
-    t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
-    hp = torch.tensor([host_pop], dtype=torch.int64, device=dev)
+    t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=cdev)
+    hp = torch.tensor([host_pop], dtype=torch.int64, device=cdev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(ident, op=dist.ReduceOp.SUM)
@@ -289,7 +292,7 @@ def bench_ours(args):
         if rank == 0:
             vgrid = (2, 2) if world == 1 else (R, C)
             v = gol_b200.GameOfLife(W, H, gen_limit=args.gens, similarity_frequency=freq, grid=vgrid, k_max=args.k,
-                                    batch_gens=args.batch, device=local_rank)
+                                    batch_gens=args.batch, device=local_rank, distributed=False)
             v.randomize(SEED)
             vres = v.run()
             verify = {"what": f"same {W}x{H} grid as {vgrid[0]}x{vgrid[1]} domains inside one process",

@@ -38,7 +38,7 @@ struct Options {
     int gen_limit = GOL_DEFAULT_GEN_LIMIT;
     int sim_freq = GOL_DEFAULT_SIMILARITY_FREQUENCY;
     int gpus = 1, ranks = 0, grid_r = 0, grid_c = 0, k = 0, batch = 0, start_gen = 0;
-    bool generic = false, lenient = false, no_write = false, stats = false, have_random = false, show = false;
+    bool generic = false, lenient = false, no_write = false, stats = false, have_random = false, show = false, cpu = false;
     unsigned long long seed = 0;
 };
 
@@ -51,16 +51,44 @@ struct Shared {  // rendezvous area shared by the forked ranks
     char blobs[64][256];
 };
 
+bool g_is_parent = false;   // the process that forked the other ranks (rank 0)
+
+// Has a forked rank died without reporting (signal, abort, non-zero exit)?  Only the parent can
+// see that; WNOWAIT leaves the child for the final waitpid in main().
+bool child_died()
+{
+    siginfo_t info;
+    memset(&info, 0, sizeof info);
+    if (waitid(P_ALL, 0, &info, WEXITED | WNOHANG | WNOWAIT) != 0 || info.si_pid == 0) return false;
+    return info.si_code != CLD_EXITED || info.si_status != 0;
+}
+
 void barrier(Shared *sh, int n)
 {
     if (n <= 1) return;
+    static const double limit_s = getenv("GOL_BARRIER_TIMEOUT_S") ? atof(getenv("GOL_BARRIER_TIMEOUT_S")) : 1800.0;
     const int gen = sh->barrier_gen;
     if (__sync_add_and_fetch(&sh->barrier_count, 1) == n) {
         sh->barrier_count = 0;
         __sync_synchronize();
         __sync_add_and_fetch(&sh->barrier_gen, 1);
     } else {
-        while (sh->barrier_gen == gen && !sh->failed) usleep(50);
+        const auto t0 = std::chrono::steady_clock::now();
+        long spins = 0;
+        while (sh->barrier_gen == gen && !sh->failed) {
+            usleep(50);
+            if ((++spins & 1023) == 0) {
+                // a rank killed by a signal never sets `failed`: the parent notices and tells everybody
+                if (g_is_parent && child_died()) {
+                    fprintf(stderr, "a rank terminated abnormally; aborting the job\n");
+                    sh->failed = 1;
+                }
+                if (std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > limit_s) {
+                    fprintf(stderr, "rank barrier timed out after %.0f s (GOL_BARRIER_TIMEOUT_S)\n", limit_s);
+                    sh->failed = 1;
+                }
+            }
+        }
     }
     if (sh->failed) exit(EXIT_FAILURE);  // another rank died: do not run on with half a job
 }
@@ -93,6 +121,8 @@ void usage()
             "  --k K --batch B          temporal depth per launch / generations per flag check\n"
             "  --start-generation G     resume: the input file is generation G of an earlier run\n"
             "  --generic                force the generic 1-generation kernel\n"
+            "  --cpu                    run on the host (threaded bit-packed CPU implementation); chosen\n"
+            "                           automatically when no CUDA device is usable\n"
             "  --lenient                bytes other than 0/1 are dead cells instead of an error\n"
             "  --random SEED            ignore the input file, start from a seeded random grid\n"
             "  --pbm PATH               also dump the final grid as a PBM image (headless show())\n"
@@ -115,6 +145,39 @@ void auto_grid(int n, long long height, int *r, int *c)
         if (n % i == 0) best = i;
     *r = best;
     *c = n / best;
+}
+
+// The whole program on the host: what the reference's serial program does (S:133-222) on a box
+// without a GPU, with the library's threaded bit-packed implementation and the same report lines.
+int run_cpu(const Options &opt)
+{
+    const bool mpi_like = is_mpi_variant(opt.variant);
+    const long long nq = (opt.width + 63) / 64;
+    std::vector<uint64_t> grid((size_t)(nq * opt.height));
+    double t0 = now_ms();
+    if (opt.have_random) {
+        if (gol_random_packed(grid.data(), opt.width, opt.height, opt.seed)) die(nullptr, "randomize");
+    } else if (gol_file_read_packed(opt.input.c_str(), opt.width, opt.height, opt.lenient ? 0 : 1, grid.data())) {
+        die(nullptr, "input");
+    }
+    if (mpi_like) printf("Reading file:\t%.2lf msecs\n", now_ms() - t0);
+    gol_result res;
+    if (opt.start_gen) fprintf(stderr, "note: --start-generation is ignored on the CPU path\n");
+    if (gol_cpu_run(grid.data(), opt.width, opt.height, opt.gen_limit, opt.sim_freq, 0, &res)) die(nullptr, "run");
+    if (opt.variant == "game") printf("Finished.\n\n");
+    if (mpi_like) printf("Generations:\t%d\nExecution time:\t%.2lf msecs\n", res.generations, res.loop_ms);
+    else if (opt.variant == "game") printf("Generations:\t%d\nExecution time:\t%.2f msecs\n", res.generations, res.loop_ms);
+    fflush(stdout);
+    t0 = now_ms();
+    if (!opt.no_write && gol_file_write_packed(opt.output.c_str(), grid.data(), opt.width, opt.height)) die(nullptr, "output");
+    if (mpi_like) printf("Writing file:\t%.2lf msecs\n", now_ms() - t0);
+    if (opt.variant == "cuda") printf("Generations:\t%d\nExecution time:\t%.2f msecs\n", res.generations, res.loop_ms);
+    if (opt.stats)
+        fprintf(stderr, "[gol] exit=%s generations=%d computed=%lld loop_ms=%.3f population=%llu path=cpu\n",
+                res.exit_reason == GOL_EXIT_EMPTY ? "empty" : res.exit_reason == GOL_EXIT_SIMILAR ? "similar" : "limit",
+                res.generations, (long long)res.generations_computed, res.loop_ms, (unsigned long long)res.population);
+    if (!opt.pbm.empty() && gol_write_pbm(opt.pbm.c_str(), grid.data(), opt.width, opt.height)) die(nullptr, "pbm");
+    return 0;
 }
 
 int run_rank(const Options &opt, int rank, int nproc, Shared *sh)
@@ -211,11 +274,12 @@ int run_rank(const Options &opt, int rank, int nproc, Shared *sh)
             const double cells = (double)opt.width * (double)opt.height;
             fprintf(stderr,
                     "[gol] exit=%s generations=%d computed=%lld loop_ms=%.3f cell_updates_per_s=%.4g population=%llu "
-                    "fast_path=%d launches=%lld\n",
+                    "fast_path=%d launches=%lld grid=%dx%d chunk_rows=%d deep_halo=%d\n",
                     res.exit_reason == GOL_EXIT_EMPTY ? "empty" : res.exit_reason == GOL_EXIT_SIMILAR ? "similar" : "limit",
                     res.generations, (long long)res.generations_computed, loop_ms,
                     cells * (double)res.generations_computed / (loop_ms * 1e-3), pop, gol_engine_uses_fast_path(eng),
-                    (long long)gol_engine_launch_count(eng));
+                    (long long)gol_engine_launch_count(eng), cfg.grid_rows, cfg.grid_cols, gol_engine_chunk_rows(eng),
+                    gol_engine_uses_deep_halo(eng));
         }
         if (opt.show && nproc == 1) {
             // the reference's show() (S:42-58, dead code there): VT100 reverse-video blocks on stdout
@@ -281,6 +345,7 @@ int main(int argc, char **argv)
         else if (a == "--batch") opt.batch = atoi(next("--batch"));
         else if (a == "--start-generation") opt.start_gen = atoi(next("--start-generation"));
         else if (a == "--generic") opt.generic = true;
+        else if (a == "--cpu") opt.cpu = true;
         else if (a == "--lenient") opt.lenient = true;
         else if (a == "--no-write") opt.no_write = true;
         else if (a == "--stats") opt.stats = true;
@@ -300,7 +365,13 @@ int main(int argc, char **argv)
         return EXIT_FAILURE;
     }
 
-    if (npos >= 3 || opt.have_random) {
+    if ((npos >= 3 || opt.have_random) && !opt.cpu && !gol_cuda_available()) {
+        fprintf(stderr, "note: no usable CUDA device; running on the host (--cpu)\n");
+        opt.cpu = true;
+    }
+    if ((npos >= 3 || opt.have_random) && opt.cpu) {
+        run_cpu(opt);
+    } else if (npos >= 3 || opt.have_random) {
         if (opt.gpus < 1) opt.gpus = 1;
         if (opt.gpus > 64) opt.gpus = 64;
         int ndom = opt.grid_r > 0 && opt.grid_c > 0 ? opt.grid_r * opt.grid_c : (opt.ranks > 0 ? opt.ranks : opt.gpus);
@@ -321,6 +392,7 @@ int main(int argc, char **argv)
         } else {
             // fork before any CUDA call: every rank creates its own context on its own GPU
             fflush(stdout);
+            g_is_parent = true;
             std::vector<pid_t> kids;
             for (int r = 1; r < nproc; ++r) {
                 pid_t pid = fork();
@@ -329,6 +401,7 @@ int main(int argc, char **argv)
                     return EXIT_FAILURE;
                 }
                 if (pid == 0) {
+                    g_is_parent = false;
                     run_rank(opt, r, nproc, sh);
                     if (mpi_like && opt.variant != "openmp") { printf("Finished\n"); fflush(stdout); }
                     _exit(0);

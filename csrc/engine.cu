@@ -23,6 +23,10 @@
 #include <fcntl.h>
 #include <sys/stat.h>
 #include <unistd.h>
+#include <atomic>
+#include <mutex>
+#include <string>
+#include <thread>
 #include <vector>
 
 #include "gol_internal.h"
@@ -53,6 +57,16 @@ struct ArenaLayout {
     std::vector<int64_t> scratch_off; // [local domain]
     int64_t rec_off = 0;
     int64_t total = 0;
+};
+
+// Text I/O staging: one lane per worker thread, two slots per lane (see io_prepare).
+struct IoSlot {
+    char *h = nullptr, *d = nullptr;   // pinned host / device staging of one row block
+    cudaEvent_t ev = nullptr;          // the device work that last used the slot
+};
+struct IoLane {
+    cudaStream_t stream = nullptr;
+    IoSlot slot[2];
 };
 
 struct IpcBlob {
@@ -94,10 +108,13 @@ struct gol_engine {
     bool deep_halo = false;         // epochs run as pairs with one 16-deep halo exchange per pair (see run_epochs)
     int pdl_mode = 2;               // GOL_PDL: 0 no programmatic dependent launch, 1 single-process engines only, 2 always
     long long wait_timeout = 0;     // device-side flag waits give up after this many clock cycles
+    bool fault_wait = false;        // GOL_FAULT_INJECT=wait: epochs wait for a flag sequence nobody publishes (tests)
     // GOL_TRACE=<n>: per-launch timeline records (first CTA start, last CTA end, flag spin cycles)
     GolTrace *d_trace = nullptr;
     int trace_cap = 0, trace_n = 0;
     std::vector<int> trace_meta;    // per record: k | mode << 8 | flags << 16
+    std::vector<IoLane> io;         // pipelined text I/O staging (allocated on first use)
+    size_t io_slot_bytes = 0;
     uint64_t *scratch_dense = nullptr;  // engine-owned dense scratch (largest local domain): randomize, population
     unsigned long long *d_count = nullptr;
 
@@ -294,6 +311,7 @@ int launch_epoch(gol_engine *e, int k, int in, int out, bool flags, int rec_slot
     lp.out_idx = out;
     static const int dbg = getenv("GOL_DEBUG_COMM") ? atoi(getenv("GOL_DEBUG_COMM")) : 0;  // timing experiments only
     lp.wait_seq = (multi(e) && mode != PAIR_SECOND && !(dbg & 4)) ? e->seq : 0;
+    if (e->fault_wait && mode != PAIR_SECOND) lp.wait_seq = e->seq + 1000;   // fault injection: the neighbours never get there
     lp.push = (mode != PAIR_FIRST ? (multi(e) ? 3 : 1) : 0) | ((dbg & 3) << 8);
     lp.seq = mode != PAIR_FIRST ? ++e->seq : e->seq;
     lp.push_rows = G;
@@ -747,6 +765,14 @@ void gol_engine_destroy(gol_engine *e)
     if (e->h_results) cudaFreeHost(e->h_results);
     if (e->d_error) cudaFree(e->d_error);
     if (e->stage) cudaFree(e->stage);
+    for (IoLane &L : e->io) {
+        for (IoSlot &S : L.slot) {
+            if (S.h) cudaFreeHost(S.h);
+            if (S.d) cudaFree(S.d);
+            if (S.ev) cudaEventDestroy(S.ev);
+        }
+        if (L.stream) cudaStreamDestroy(L.stream);
+    }
     if (e->d_trace) cudaFree(e->d_trace);
     if (e->scratch_dense) cudaFree(e->scratch_dense);
     if (e->d_count) cudaFree(e->d_count);
@@ -792,6 +818,8 @@ static int engine_create_impl(gol_engine *e)
     GOL_CUDA(cudaEventCreateWithFlags(&e->ev_slot[1], cudaEventDisableTiming));
 
     GOL_CUDA(cudaMalloc(&e->d_count, 8));
+    GOL_CUDA(cudaMalloc(&e->d_error, 2 * sizeof(unsigned int)));   // [0] sticky wait-timeout word, [1] text parse errors
+    GOL_CUDA(cudaMemset(e->d_error, 0, 2 * sizeof(unsigned int)));
     if (!e->fast) {
         const size_t bytes = (size_t)(gol_div_up(cfg.width, 64) * cfg.height) * sizeof(uint64_t);
         for (auto &d : e->dense) {
@@ -845,6 +873,7 @@ static int engine_create_impl(gol_engine *e)
         const double ms = v ? atof(v) : 20000.0;
         e->wait_timeout = (long long)(std::max(1.0, ms) * (double)prop.clockRate);  // clockRate is in kHz = cycles per ms
     }
+    if (const char *v = getenv("GOL_FAULT_INJECT")) e->fault_wait = strcmp(v, "wait") == 0;
     if (const char *v = getenv("GOL_TRACE")) {
         e->trace_cap = std::max(0, atoi(v));
         if (e->trace_cap) {
@@ -864,8 +893,6 @@ static int engine_create_impl(gol_engine *e)
     GOL_CUDA(cudaMalloc(&e->d_results, sizeof(unsigned long long) * (kMaxBatch + 2)));
     GOL_CUDA(cudaMemset(e->d_results, 0, sizeof(unsigned long long) * (kMaxBatch + 2)));
     GOL_CUDA(cudaMallocHost(&e->h_results, sizeof(unsigned long long) * (kMaxBatch + 2)));
-    GOL_CUDA(cudaMalloc(&e->d_error, 2 * sizeof(unsigned int)));
-    GOL_CUDA(cudaMemset(e->d_error, 0, 2 * sizeof(unsigned int)));
     {
         size_t stage_bytes = 0;
         for (const LocalDomain &ld : e->local) {
@@ -1242,6 +1269,160 @@ int gol_engine_hash(gol_engine *e, uint64_t *hash)
     return 0;
 }
 
+// ------------------------------------------------------------ text file I/O
+// Pipelined staging for the text reader and writer.  A few worker threads ("lanes") split the row
+// blocks of a domain between them; each lane owns a CUDA stream and two pinned host / device slot
+// pairs, so that on every lane the file system call of one block (pread / pwrite, a CPU-speed copy
+// out of or into the page cache) overlaps the PCIe copy and the parse / format kernel of the next
+// or previous block, and the lanes run their system calls in parallel.  The slots belong to the
+// engine and are allocated on first use (replaces the non-blocking and collective MPI-IO of
+// A:186-198, A:428-448, C:190-198, C:425-445: there the wait follows the request immediately).
+}  // extern "C"
+
+namespace {
+
+int io_prepare(gol_engine *e)
+{
+    if (!e->io.empty()) return 0;
+    int lanes = 4;
+    if (const char *v = getenv("GOL_IO_THREADS")) lanes = std::max(1, std::min(16, atoi(v)));
+    e->io_slot_bytes = 8u << 20;
+    if (const char *v = getenv("GOL_IO_SLOT_MB")) e->io_slot_bytes = (size_t)std::max(1, atoi(v)) << 20;
+    // a slot holds at least one full line of the file
+    e->io_slot_bytes = std::max<size_t>(e->io_slot_bytes, (size_t)e->cfg.width + 64);
+    e->io.resize((size_t)lanes);
+    for (IoLane &L : e->io) {
+        GOL_CUDA(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
+        for (IoSlot &S : L.slot) {
+            GOL_CUDA(cudaMallocHost(&S.h, e->io_slot_bytes));
+            GOL_CUDA(cudaMalloc(&S.d, e->io_slot_bytes));
+            GOL_CUDA(cudaEventCreateWithFlags(&S.ev, cudaEventDisableTiming));
+        }
+    }
+    return 0;
+}
+
+// read exactly `want` bytes at `pos`
+bool pread_all(int fd, char *dst, int64_t want, int64_t pos, std::string *err, const char *path)
+{
+    int64_t off = 0;
+    while (off < want) {
+        const ssize_t got = pread(fd, dst + off, (size_t)(want - off), (off_t)(pos + off));
+        if (got <= 0) {
+            if (got < 0 && errno == EINTR) continue;
+            *err = std::string("read: ") + path + ": " + (got < 0 ? strerror(errno) : "unexpected end of file");
+            return false;
+        }
+        off += got;
+    }
+    return true;
+}
+
+struct IoJob {
+    gol_engine *e;
+    int fd;
+    const char *path;
+    int64_t file_size, W;            // global line length is W + 1
+    int64_t x0, y0, w, h;            // the block of the grid this job moves
+    uint64_t *d_dense;               // packed dense rows of the block on the device
+    uint32_t *d_err;                 // parse errors (reader)
+    std::mutex mu;
+    std::string error;
+    std::atomic<int> failed{0};
+    void fail(const std::string &msg)
+    {
+        std::lock_guard<std::mutex> g(mu);
+        if (!failed.exchange(1)) error = msg;
+    }
+};
+
+void io_read_lane(IoJob *J, int lane_id, int lanes)
+{
+    gol_engine *e = J->e;
+    IoLane &L = e->io[(size_t)lane_id];
+    if (cudaSetDevice(e->cfg.device) != cudaSuccess) return J->fail("cudaSetDevice failed in an I/O thread");
+    const bool last_col = J->x0 + J->w == J->W, whole_rows = J->x0 == 0 && last_col;
+    const int64_t seg = J->w + (last_col ? 1 : 0);  // bytes per row of this block (newline owned by the last column)
+    const int64_t rows_per = std::max<int64_t>(1, (int64_t)e->io_slot_bytes / seg);
+    const int64_t chunks = gol_div_up(J->h, rows_per), nq = gol_div_up(J->w, 64);
+    int use = 0;
+    for (int64_t c = lane_id; c < chunks && !J->failed; c += lanes, use ^= 1) {
+        IoSlot &S = L.slot[use];
+        if (cudaEventSynchronize(S.ev) != cudaSuccess) return J->fail("I/O slot event failed");  // its last H2D + parse are done
+        const int64_t r = c * rows_per, n = std::min(rows_per, J->h - r);
+        std::string err;
+        if (whole_rows) {  // one contiguous range of the file
+            int64_t want = n * seg;
+            const int64_t pos = (J->y0 + r) * (J->W + 1);
+            if (pos + want > J->file_size) {  // no newline after the very last line
+                want = J->file_size - pos;
+                S.h[n * seg - 1] = '\n';
+            }
+            if (!pread_all(J->fd, S.h, want, pos, &err, J->path)) return J->fail(err);
+        } else {
+            for (int64_t k = 0; k < n; ++k) {
+                int64_t want = seg;
+                const int64_t pos = (J->y0 + r + k) * (J->W + 1) + J->x0;
+                if (pos + want > J->file_size) { want = J->file_size - pos; S.h[k * seg + seg - 1] = '\n'; }
+                if (!pread_all(J->fd, S.h + k * seg, want, pos, &err, J->path)) return J->fail(err);
+            }
+        }
+        if (cudaMemcpyAsync(S.d, S.h, (size_t)(n * seg), cudaMemcpyHostToDevice, L.stream) != cudaSuccess)
+            return J->fail("H2D copy of a text block failed");
+        if (gol_op_parse_text_n(S.d, n * seg, J->d_dense + r * nq, J->w, n, seg, J->d_err, L.stream)) return J->fail(gol_last_error());
+        cudaEventRecord(S.ev, L.stream);
+    }
+    if (cudaStreamSynchronize(L.stream) != cudaSuccess) J->fail("parse kernel failed");
+}
+
+void io_write_lane(IoJob *J, int lane_id, int lanes)
+{
+    gol_engine *e = J->e;
+    IoLane &L = e->io[(size_t)lane_id];
+    if (cudaSetDevice(e->cfg.device) != cudaSuccess) return J->fail("cudaSetDevice failed in an I/O thread");
+    const bool last_col = J->x0 + J->w == J->W, whole_rows = J->x0 == 0 && last_col;
+    const int64_t seg = J->w + (last_col ? 1 : 0);
+    const int64_t rows_per = std::max<int64_t>(1, (int64_t)e->io_slot_bytes / seg);
+    const int64_t chunks = gol_div_up(J->h, rows_per), nq = gol_div_up(J->w, 64);
+    auto issue = [&](int64_t c, IoSlot &S) -> bool {  // format block c on the device and start bringing it home
+        const int64_t r = c * rows_per, n = std::min(rows_per, J->h - r);
+        if (gol_op_format_text(J->d_dense + r * nq, S.d, J->w, n, seg, last_col ? 1 : 0, L.stream)) { J->fail(gol_last_error()); return false; }
+        if (cudaMemcpyAsync(S.h, S.d, (size_t)(n * seg), cudaMemcpyDeviceToHost, L.stream) != cudaSuccess) { J->fail("D2H copy of a text block failed"); return false; }
+        cudaEventRecord(S.ev, L.stream);
+        return true;
+    };
+    int use = 0;
+    if (lane_id < chunks && !issue(lane_id, L.slot[0])) return;
+    for (int64_t c = lane_id; c < chunks && !J->failed; c += lanes, use ^= 1) {
+        if (c + lanes < chunks && !issue(c + lanes, L.slot[use ^ 1])) return;  // next block formats while this one is written
+        IoSlot &S = L.slot[use];
+        if (cudaEventSynchronize(S.ev) != cudaSuccess) return J->fail("format kernel / D2H copy failed");
+        const int64_t r = c * rows_per, n = std::min(rows_per, J->h - r);
+        if (whole_rows) {
+            if (gol_write_all(J->fd, S.h, (size_t)(n * seg), (J->y0 + r) * (J->W + 1), J->path)) return J->fail(gol_last_error());
+        } else {
+            for (int64_t k = 0; k < n; ++k)
+                if (gol_write_all(J->fd, S.h + k * seg, (size_t)seg, (J->y0 + r + k) * (J->W + 1) + J->x0, J->path))
+                    return J->fail(gol_last_error());
+        }
+    }
+}
+
+int io_run(IoJob *J, bool reading)
+{
+    const int lanes = (int)J->e->io.size();
+    std::vector<std::thread> pool;
+    for (int t = 1; t < lanes; ++t) pool.emplace_back(reading ? io_read_lane : io_write_lane, J, t, lanes);
+    (reading ? io_read_lane : io_write_lane)(J, 0, lanes);
+    for (auto &th : pool) th.join();
+    if (J->failed) GOL_FAIL("%s", J->error.c_str());
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
 // Parallel text read: every process reads only its own byte ranges.  The file must be in
 // the fixed-record layout (height lines of exactly width cells + '\n'), which is what
 // generate.sh and every writer of the reference produce; other layouts go through
@@ -1272,85 +1453,42 @@ int gol_engine_load_text_file(gol_engine *e, const char *path, int strict)
         return gol_engine_load_packed(e, packed.data());
     }
     GOL_TRY(clear_current(e));
-    int rc = 0;
+    int rc = io_prepare(e);
+    uint32_t *d_err = e->d_error + 1;
+    if (!rc && cudaMemsetAsync(d_err, 0, 4, e->stream) != cudaSuccess) rc = 1;
+    if (!rc && cudaStreamSynchronize(e->stream) != cudaSuccess) rc = 1;
     const int ndom_local = e->fast ? e->per_proc : 1;
     for (int i = 0; i < ndom_local && !rc; ++i) {
-        int64_t x0 = 0, y0 = 0, w = W, h = H;
+        IoJob J;
+        J.e = e; J.fd = fd; J.path = path; J.file_size = st.st_size; J.W = W;
+        J.x0 = 0; J.y0 = 0; J.w = W; J.h = H;
+        J.d_err = d_err;
         if (e->fast) {
             const LocalDomain &ld = e->local[(size_t)i];
-            x0 = ld.x0; y0 = ld.y0; w = ld.L.width; h = ld.L.height;
+            J.x0 = ld.x0; J.y0 = ld.y0; J.w = ld.L.width; J.h = ld.L.height;
+            J.d_dense = e->scratch_dense;
+        } else {
+            J.d_dense = e->dense[e->cur];
         }
-        const bool last_col = x0 + w == W;
-        const int64_t seg = w + (last_col ? 1 : 0);  // bytes per row of this domain (newline owned by last column)
-        const int64_t rows_per = std::max<int64_t>(1, std::min<int64_t>(h, (64ll << 20) / seg));
-        char *h_stage = nullptr, *d_stage = nullptr;
-        uint64_t *d_dense = nullptr;
-        uint32_t *d_err = nullptr;
-        const int64_t nq = gol_div_up(w, 64);
-        if (cudaMallocHost(&h_stage, (size_t)(rows_per * seg)) != cudaSuccess ||
-            cudaMalloc(&d_stage, (size_t)(rows_per * seg)) != cudaSuccess ||
-            cudaMalloc(&d_dense, (size_t)(nq * h) * 8) != cudaSuccess || cudaMalloc(&d_err, 4) != cudaSuccess) {
-            gol_set_error("out of memory staging %s", path);
+        rc = io_run(&J, true);
+        if (!rc && e->fast) {
+            const LocalDomain &ld = e->local[(size_t)i];
+            char *dst = e->arena + e->arena_layout.buf_off[(size_t)i * GOL_NBUF + e->cur];
+            if (cudaMemsetAsync(dst, 0, (size_t)ld.L.buffer_words32 * 4, e->stream) != cudaSuccess) rc = 1;
+            if (!rc) rc = gol_launch_dense_to_padded(e->scratch_dense, ld.L.nq, 0, reinterpret_cast<uint32_t *>(dst), ld.L, e->stream);
+            ++e->launches;
+            if (!rc && cudaStreamSynchronize(e->stream) != cudaSuccess) { gol_set_error("dense_to_padded failed"); rc = 1; }
+        }
+    }
+    if (!rc) {
+        uint32_t err = 0;
+        cudaMemcpy(&err, d_err, 4, cudaMemcpyDeviceToHost);
+        if ((err & 2) || ((err & 1) && strict)) {
+            gol_set_error("%s: %s", path, (err & 2) ? "a line does not end in a newline at column width (garbled record layout)"
+                                                   : "invalid byte: only '0', '1' and newlines are accepted");
             rc = 1;
         }
-        if (!rc) cudaMemsetAsync(d_err, 0, 4, e->stream);
-        for (int64_t r = 0; r < h && !rc; r += rows_per) {
-            const int64_t n = std::min(rows_per, h - r);
-            if (x0 == 0 && last_col) {
-                // whole rows: one contiguous range
-                int64_t want = n * seg;
-                if ((y0 + r + n) * (W + 1) > st.st_size) want = st.st_size - (y0 + r) * (W + 1);  // no final newline
-                int64_t off = 0;
-                while (off < want) {
-                    ssize_t got = pread(fd, h_stage + off, (size_t)(want - off), (off_t)((y0 + r) * (W + 1) + off));
-                    if (got <= 0) { if (got < 0 && errno == EINTR) continue; gol_set_error("read: %s: %s", path, got < 0 ? strerror(errno) : "unexpected end of file"); rc = 1; break; }
-                    off += got;
-                }
-                if (want < n * seg) h_stage[n * seg - 1] = '\n';
-            } else {
-                for (int64_t k = 0; k < n && !rc; ++k) {
-                    int64_t want = seg;
-                    const int64_t pos = (y0 + r + k) * (W + 1) + x0;
-                    if (pos + want > st.st_size) { want = st.st_size - pos; h_stage[k * seg + seg - 1] = '\n'; }
-                    int64_t off = 0;
-                    while (off < want) {
-                        ssize_t got = pread(fd, h_stage + k * seg + off, (size_t)(want - off), (off_t)(pos + off));
-                        if (got <= 0) { if (got < 0 && errno == EINTR) continue; gol_set_error("read: %s: %s", path, got < 0 ? strerror(errno) : "unexpected end of file"); rc = 1; break; }
-                        off += got;
-                    }
-                }
-            }
-            if (rc) break;
-            if (cudaMemcpyAsync(d_stage, h_stage, (size_t)(n * seg), cudaMemcpyHostToDevice, e->stream) != cudaSuccess) { gol_set_error("H2D copy failed"); rc = 1; break; }
-            rc = gol_op_parse_text(d_stage, d_dense + r * nq, w, n, seg, d_err, e->stream);
-            ++e->launches;
-            if (!rc && cudaStreamSynchronize(e->stream) != cudaSuccess) { gol_set_error("parse kernel failed: %s", cudaGetErrorString(cudaGetLastError())); rc = 1; }
-        }
-        if (!rc) {
-            uint32_t err = 0;
-            cudaMemcpy(&err, d_err, 4, cudaMemcpyDeviceToHost);
-            if ((err & 2) || ((err & 1) && strict)) {
-                gol_set_error("%s: %s", path, (err & 2) ? "a line does not end in a newline at column width (garbled record layout)"
-                                                       : "invalid byte: only '0', '1' and newlines are accepted");
-                rc = 1;
-            }
-        }
-        if (!rc) {
-            if (e->fast) {
-                const LocalDomain &ld = e->local[(size_t)i];
-                char *dst = e->arena + e->arena_layout.buf_off[(size_t)i * GOL_NBUF + e->cur];
-                if (cudaMemsetAsync(dst, 0, (size_t)ld.L.buffer_words32 * 4, e->stream) != cudaSuccess) rc = 1;
-                if (!rc) rc = gol_launch_dense_to_padded(d_dense, nq, 0, reinterpret_cast<uint32_t *>(dst), ld.L, e->stream);
-                ++e->launches;
-            } else {
-                if (cudaMemcpyAsync(e->dense[e->cur], d_dense, (size_t)(nq * h) * 8, cudaMemcpyDeviceToDevice, e->stream) != cudaSuccess) rc = 1;
-            }
-            cudaStreamSynchronize(e->stream);
-        }
-        if (h_stage) cudaFreeHost(h_stage);
-        if (d_stage) cudaFree(d_stage);
-        if (d_dense) cudaFree(d_dense);
-        if (d_err) cudaFree(d_err);
+        cudaMemset(d_err, 0, 4);
     }
     close(fd);
     return rc;
@@ -1367,58 +1505,25 @@ int gol_engine_store_text_file(gol_engine *e, const char *path)
         close(fd);
         GOL_FAIL("ftruncate: %s: %s", path, strerror(errno));
     }
-    int rc = 0;
+    int rc = io_prepare(e);
     const int ndom_local = e->fast ? e->per_proc : 1;
     for (int i = 0; i < ndom_local && !rc; ++i) {
-        int64_t x0 = 0, y0 = 0, w = W, h = H;
+        IoJob J;
+        J.e = e; J.fd = fd; J.path = path; J.file_size = H * (W + 1); J.W = W;
+        J.x0 = 0; J.y0 = 0; J.w = W; J.h = H;
+        J.d_err = nullptr;
         if (e->fast) {
             const LocalDomain &ld = e->local[(size_t)i];
-            x0 = ld.x0; y0 = ld.y0; w = ld.L.width; h = ld.L.height;
-        }
-        const bool last_col = x0 + w == W;
-        const int64_t seg = w + (last_col ? 1 : 0);
-        const int64_t rows_per = std::max<int64_t>(1, std::min<int64_t>(h, (64ll << 20) / seg));
-        const int64_t nq = gol_div_up(w, 64);
-        char *h_stage = nullptr, *d_stage = nullptr;
-        uint64_t *d_dense = nullptr;
-        if (cudaMallocHost(&h_stage, (size_t)(rows_per * seg)) != cudaSuccess ||
-            cudaMalloc(&d_stage, (size_t)(rows_per * seg)) != cudaSuccess) {
-            gol_set_error("out of memory staging %s", path);
-            rc = 1;
-        }
-        const uint64_t *dense = nullptr;
-        if (!rc) {
-            if (e->fast) {
-                const LocalDomain &ld = e->local[(size_t)i];
-                if (cudaMalloc(&d_dense, (size_t)(nq * h) * 8) != cudaSuccess) { gol_set_error("out of memory"); rc = 1; }
-                const char *src = e->arena + e->arena_layout.buf_off[(size_t)i * GOL_NBUF + e->cur];
-                if (!rc) rc = gol_launch_padded_to_dense(reinterpret_cast<const uint32_t *>(src), ld.L, d_dense, nq, 0, 0, e->stream);
-                ++e->launches;
-                dense = d_dense;
-            } else {
-                dense = e->dense[e->cur];
-            }
-        }
-        for (int64_t r = 0; r < h && !rc; r += rows_per) {
-            const int64_t n = std::min(rows_per, h - r);
-            rc = gol_op_format_text(dense + r * nq, d_stage, w, n, seg, last_col ? 1 : 0, e->stream);
+            J.x0 = ld.x0; J.y0 = ld.y0; J.w = ld.L.width; J.h = ld.L.height;
+            const char *src = e->arena + e->arena_layout.buf_off[(size_t)i * GOL_NBUF + e->cur];
+            rc = gol_launch_padded_to_dense(reinterpret_cast<const uint32_t *>(src), ld.L, e->scratch_dense, ld.L.nq, 0, 0, e->stream);
             ++e->launches;
-            if (!rc && (cudaMemcpyAsync(h_stage, d_stage, (size_t)(n * seg), cudaMemcpyDeviceToHost, e->stream) != cudaSuccess ||
-                        cudaStreamSynchronize(e->stream) != cudaSuccess)) {
-                gol_set_error("format kernel / D2H copy failed: %s", cudaGetErrorString(cudaGetLastError()));
-                rc = 1;
-            }
-            if (rc) break;
-            if (x0 == 0 && last_col) {
-                rc = gol_write_all(fd, h_stage, (size_t)(n * seg), (y0 + r) * (W + 1), path);
-            } else {
-                for (int64_t k = 0; k < n && !rc; ++k)
-                    rc = gol_write_all(fd, h_stage + k * seg, (size_t)seg, (y0 + r + k) * (W + 1) + x0, path);
-            }
+            J.d_dense = e->scratch_dense;
+        } else {
+            J.d_dense = e->dense[e->cur];
         }
-        if (h_stage) cudaFreeHost(h_stage);
-        if (d_stage) cudaFree(d_stage);
-        if (d_dense) cudaFree(d_dense);
+        if (!rc && cudaStreamSynchronize(e->stream) != cudaSuccess) { gol_set_error("padded_to_dense failed"); rc = 1; }
+        if (!rc) rc = io_run(&J, false);
     }
     close(fd);
     return rc;

@@ -82,6 +82,7 @@ def _proto(lib):
         "gol_op_pack_cells": (i32, [vp, vp, i64, i64, vp]),
         "gol_op_unpack_cells": (i32, [vp, vp, i64, i64, vp]),
         "gol_op_parse_text": (i32, [vp, vp, i64, i64, i64, vp, vp]),
+        "gol_op_parse_text_n": (i32, [vp, i64, vp, i64, i64, i64, vp, vp]),
         "gol_op_format_text": (i32, [vp, vp, i64, i64, i64, i32, vp]),
         "gol_op_random_dense": (i32, [vp, i64, i64, i64, i64, u64, vp]),
         "gol_op_popcount_dense": (i32, [vp, i64, i64, vp, vp]),

@@ -58,7 +58,10 @@ class _DeviceBuffer:
 
 class GameOfLife:
     def __init__(self, width: int | None = None, height: int | None = None, *, config: LifeConfig | None = None,
-                 device: int | None = None, process_group=None, **overrides):
+                 device: int | None = None, process_group=None, distributed: bool | None = None, **overrides):
+        """`distributed`: None = one rank of the default process group when torch.distributed is
+        initialised and a decomposition is given (or `process_group` is passed); False = every
+        domain lives in this process even inside a distributed job (no collective is issued)."""
         import torch
         N.require_cuda()
         cfg = config or LifeConfig()
@@ -75,7 +78,9 @@ class GameOfLife:
         self._group = process_group
         rank, world = 0, 1
         import torch.distributed as dist
-        if process_group is not None or (dist.is_available() and dist.is_initialized() and cfg.grid != (1, 1)):
+        if distributed is None:
+            distributed = process_group is not None or (dist.is_available() and dist.is_initialized() and cfg.grid != (1, 1))
+        if distributed:
             rank, world = dist.get_rank(process_group), dist.get_world_size(process_group)
         self.rank, self.world = rank, world
         if device is None:

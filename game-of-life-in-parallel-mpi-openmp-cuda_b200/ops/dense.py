@@ -100,8 +100,8 @@ def parse_text(text: torch.Tensor, width: int, height: int, pitch: int | None = 
     out = torch.empty((height, words_per_row(width)), dtype=torch.int64, device=text.device)
     err = torch.zeros(1, dtype=torch.int32, device=text.device)
     with torch.cuda.device(text.device):
-        N.check(N.lib().gol_op_parse_text(text.data_ptr(), out.data_ptr(), width, height, pitch,
-                                          err.data_ptr(), _stream()), "parse_text")
+        N.check(N.lib().gol_op_parse_text_n(text.data_ptr(), text.numel(), out.data_ptr(), width, height, pitch,
+                                            err.data_ptr(), _stream()), "parse_text")
     code = int(err.item())
     if code & 2:
         raise N.GolError("parse_text: a line does not end in a newline at column `width`")

@@ -24,6 +24,12 @@ PATTERNS = {
     ],
     # a diagonal of three cells: dies in exactly two generations
     "diag3": ["100", "010", "001"],
+    # "die hard": vanishes completely after 130 generations (empty exit deep inside a batch)
+    "diehard": ["00000010", "11000000", "01000111"],
+    # a 12 x 12 soup (found by search with the CPU oracle) that settles into still lifes only: on an empty
+    # torus of at least 384 x 384 the reference loop reports Generations: 590 through the similarity exit
+    "late590": ["110011011100", "001100001100", "100101000010", "111001111011", "010011100010", "001011001001",
+                "110101011010", "110010101110", "001001011000", "110010101111", "100000100111", "110101010000"],
 }
 
 

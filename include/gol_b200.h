@@ -142,6 +142,11 @@ int gol_op_unpack_cells(const uint64_t *d_packed, uint8_t *d_cells, int64_t widt
  * missing newline. */
 int gol_op_parse_text(const char *d_text, uint64_t *d_packed, int64_t width, int64_t height,
                       int64_t text_pitch, uint32_t *d_err, void *stream);
+/* Same with the length of the text buffer: the newline of a row is only checked where the buffer
+ * has a byte at column `width` (a last line without a newline is accepted), and nothing outside
+ * [d_text, d_text + text_bytes) is read. */
+int gol_op_parse_text_n(const char *d_text, int64_t text_bytes, uint64_t *d_packed, int64_t width,
+                        int64_t height, int64_t text_pitch, uint32_t *d_err, void *stream);
 int gol_op_format_text(const uint64_t *d_packed, char *d_text, int64_t width, int64_t height,
                        int64_t text_pitch, int newline, void *stream);
 int gol_op_random_dense(uint64_t *d_packed, int64_t width, int64_t height, int64_t x0, int64_t y0,

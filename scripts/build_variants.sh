@@ -1,14 +1,14 @@
 #!/bin/bash
-# Builds kernel-variant libraries for A/B timing: variants/libgol_s<SKEW>_o<ONE_SIDED>.so
-# (run a variant with GOL_LIB=variants/libgol_s1_o1.so python scripts/profile_step.py ...)
+# Builds the experiment binaries (not part of `make all`; nothing here is linked into libgolb200.so):
+#   bin/gol-tilebench   TMA-fed cluster/DSMEM tile kernel against the product's register pipeline
+#                       (csrc/experiments/life_tile.cu)
+# The round-1 kernel variants (skewed levels, IMAD shifts, warp-pipelined FIFOs, persistent dataflow
+# kernel) are kept for the record in csrc/experiments/life_kernels_r1_variants.cu; they were written
+# against the round-1 engine interface and are no longer built.
 set -e
 cd "$(dirname "$0")/.."
-mkdir -p variants build
+mkdir -p bin
 ARCH="-gencode arch=compute_100a,code=sm_100a"
-for s in 0 1; do for o in 0 1; do
-  nvcc $ARCH -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -DGOL_SKEW=$s -DGOL_ONE_SIDED=$o -c csrc/life_kernels.cu -o build/life_kernels_s${s}_o${o}.o &
-done; done; wait
-for s in 0 1; do for o in 0 1; do
-  nvcc $ARCH -shared -o variants/libgol_s${s}_o${o}.so build/life_kernels_s${s}_o${o}.o build/dense_kernels.o build/engine.o build/static_scratch.o build/host_util.o
-done; done
-ls -la variants
+nvcc $ARCH -O3 -std=c++17 -lineinfo -Xptxas -v -Iinclude csrc/experiments/life_tile.cu -o bin/gol-tilebench 2> build/life_tile.ptxas.log || { cat build/life_tile.ptxas.log; exit 1; }
+grep -E "life_tile_kernel|registers|spill" build/life_tile.ptxas.log | grep -A1 "life_tile_kernel" | grep -E "registers" | sort | uniq -c
+ls -la bin/gol-tilebench

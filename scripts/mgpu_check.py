@@ -111,6 +111,22 @@ res = life.run()
 t = torch.tensor([res.loop_ms], device="cuda", dtype=torch.float64)
 dist.all_reduce(t, op=dist.ReduceOp.MAX)
 log(f"[time] run() {res.generations} generations: {t.item():.3f} ms -> "
-    f"{W * H * res.generations_computed / t.item() / 1e9:.2f} T cell-updates/s")
+    f"{W * H * res.generations_computed / t.item() / 1e9:.2f} T cell-updates/s "
+    f"(grid {R}x{C}, chunk_rows {life.chunk_rows}, deep halo {life.uses_deep_halo})")
+# identity of the final grid: checksum summed over the ranks == the same grid run inside one process
+lh = life.local_hash()
+ident = torch.tensor([lh - (1 << 64) if lh >= (1 << 63) else lh, life.population()], dtype=torch.int64, device="cuda")
+dist.all_reduce(ident, op=dist.ReduceOp.SUM)
 life.close()
+if not a.skip_check and W * H <= (1 << 34):
+    if rank == 0:
+        one = gol_b200.GameOfLife(W, H, grid=(1, 1), device=local, similarity_frequency=3, gen_limit=1000)
+        one.randomize(1)
+        r1 = one.run()
+        same = (one.local_hash() == (int(ident[0].item()) & ((1 << 64) - 1)) and one.population() == int(ident[1].item())
+                and r1.generations == res.generations)
+        one.close()
+        assert same, "multi-process result differs from the single-process run"
+        log("[check] checksum equals the single-process run of the same grid")
+    dist.barrier()
 dist.destroy_process_group()

@@ -37,6 +37,28 @@ def test_strip_kernel_matches_cpu(cuda_device, w, h):
     check_steps(w, h, [1, 2, 3, 5, 8, 16, 23])
 
 
+@pytest.mark.parametrize("w,h,gens,grid", [(16384, 16384, 64, (1, 1)), (65536, 2048, 40, (1, 1)), (16384, 16384, 48, (2, 2))])
+def test_benchmark_geometry_matches_oracle(cuda_device, w, h, gens, grid):
+    # the shapes bench.py and BASELINE config 3 time: 512- / 2048-word rows (9 / 35 strips with the
+    # right-aligned overlapping last strip), more chunks than resident warps, the AUTOTUNED chunk
+    # height (only active from 256 rows up), programmatic dependent launch between the epochs
+    from gol_b200.ops import cpu
+    start = cpu.random_grid(w, h, 11)
+    life = make(w, h, grid=grid, gen_limit=gens + 8)
+    life.load_packed(start)
+    assert life.uses_fast_path and life.chunk_rows >= 16
+    life.step(gens)
+    want = cpu.step(start, w, gens)
+    assert np.array_equal(life.packed_numpy(), want)
+    assert life.local_hash() == cpu.grid_hash(want, w)
+    life.load_packed(start)                      # and the reference loop (flag epochs, gather, batches)
+    res = life.run()
+    wantg, wres = cpu.run(start, w, gen_limit=gens + 8)
+    assert (res.generations, res.population) == (wres.generations, wres.population)
+    assert life.local_hash() == cpu.grid_hash(wantg, w)
+    life.close()
+
+
 @pytest.mark.parametrize("k", [1, 2, 4, 8, 16])
 def test_temporal_depths(cuda_device, k):
     check_steps(1100, 200, [k, 3 * k + 1, 37], k_max=k)
@@ -96,6 +118,16 @@ def test_run_semantics_fixtures(cuda_device):
         for kw in ({}, {"grid": (2, 2)}, {"k_max": 8, "batch_gens": 24}, {"similarity_frequency": 0, "gen_limit": 50},
                    {"similarity_frequency": 5}, {"gen_limit": 7}):
             run_both(cells, **kw)
+
+
+def test_late_exits_deep_inside_a_batch(cuda_device):
+    # exits far from a batch boundary: the speculative driver overshoots, replays the batch one generation
+    # at a time and must still report the serial loop's exact Generations value and grid
+    from gol_b200.utils import patterns
+    r = run_both(patterns.grid_with(1024, 1024, ("late590", 506, 506)))
+    assert (r.generations, r.exit_reason) == (590, "similar")
+    r = run_both(patterns.grid_with(1024, 512, ("diehard", 500, 250)), grid=(2, 1))
+    assert (r.generations, r.exit_reason) == (130, "empty")
 
 
 def test_run_stabilising_at_every_residue(cuda_device):

@@ -44,6 +44,25 @@ def test_step_dense_matches_conv2d(cuda_device, w, h):
         packed, cur = nxt, want
 
 
+def test_strip_kernel_matches_conv2d(cuda_device):
+    # the PRODUCT kernel (register-pipelined strips, temporal blocking, fused torus wrap) against the
+    # plain PyTorch fp32 oracle, ragged width and several temporal depths
+    import gol_b200
+    g = torch.Generator(device="cpu").manual_seed(99)
+    for w, h, k in [(840, 200, 8), (1000, 70, 4), (2112, 96, 8)]:
+        cells = (torch.rand((h, w), generator=g) < 0.37).to(torch.uint8).to(cuda_device)
+        life = gol_b200.GameOfLife(w, h, device=0, k_max=k)
+        assert life.uses_fast_path
+        life.load(cells)
+        want = cells
+        for n in (1, k, k + 3):
+            life.step(n)
+            for _ in range(n):
+                want = conv_oracle(want)
+            assert torch.equal(life.cells(), want), (w, h, k, n)
+        life.close()
+
+
 def test_flags_empty_similar(cuda_device):
     from gol_b200.ops import dense
     z = torch.zeros((5, 2), dtype=torch.int64, device=cuda_device)
@@ -73,6 +92,35 @@ def test_parse_format_random_match_cpu(cuda_device):
     bad[2, 1025] = ord("0")
     with pytest.raises(Exception, match="newline"):
         dense.parse_text(bad, 1025, 5)
+
+
+def test_text_kernels_every_alignment_and_ragged_tail(cuda_device):
+    """The vectorised parse / format kernels against plain PyTorch: rows of W+1 bytes start at every
+    byte alignment, widths that end inside a word / a 16-byte vector / a 8192-cell segment, buffers
+    that are slices at odd offsets, and a last line without a newline (nothing past it is read)."""
+    from gol_b200.ops import dense
+    g = torch.Generator(device="cpu").manual_seed(77)
+    for w, h in [(1, 3), (15, 4), (16, 5), (17, 33), (31, 2), (33, 17), (100, 9), (8191, 3), (8192, 2), (8193, 5), (20000, 3)]:
+        cells = (torch.rand((h, w), generator=g) < 0.5).to(torch.uint8).to(cuda_device)
+        packed = dense.pack_cells(cells)
+        # plain PyTorch reference of the packing: bit i of word q = cell 64 q + i
+        nq = (w + 63) // 64
+        padded = torch.zeros((h, nq * 64), dtype=torch.int64, device=cuda_device)
+        padded[:, :w] = cells
+        want = (padded.view(h, nq, 64) << torch.arange(64, device=cuda_device)).sum(dim=2)   # wraps mod 2^64
+        assert torch.equal(packed, want), (w, h)
+        assert torch.equal(dense.unpack_cells(packed, w), cells)
+        text = dense.format_text(packed, w)
+        want_text = torch.full((h, w + 1), ord("\n"), dtype=torch.uint8, device=cuda_device)
+        want_text[:, :w] = cells + ord("0")
+        assert torch.equal(text, want_text), (w, h)
+        for off in (0, 1, 3, 7, 13):                       # the buffer itself starts at an odd address
+            big = torch.full((off + text.numel() + 64,), ord("x"), dtype=torch.uint8, device=cuda_device)
+            big[off:off + text.numel()] = text.flatten()
+            assert torch.equal(dense.parse_text(big[off:off + text.numel()], w, h), packed), (w, h, off)
+            # no newline after the last line: the byte after the buffer is an 'x' that must not be looked at
+            assert torch.equal(dense.parse_text(big[off:off + text.numel() - 1], w, h), packed), (w, h, off)
+        assert torch.equal(dense.format_text(packed, w, newline=False), want_text[:, :w].contiguous())
 
 
 def test_custom_op_and_module(cuda_device):
