@@ -130,6 +130,8 @@ struct gol_engine {
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_slot[2] = {nullptr, nullptr}, ev_tune[2] = {nullptr, nullptr};
+    cudaStream_t flag_stream = nullptr;   // flag gathers + their read-back run beside the generation stream
+    cudaEvent_t ev_flag[2] = {nullptr, nullptr};
     double last_ms = 0.0;
     int kmax = 8, batch = 128;
 };
@@ -262,6 +264,8 @@ void geometry(const gol_engine *e, int k, GolLaunch *lp, int ext_y = 0, int ext_
     lp->edge_rows = E;
     lp->ext_y = ext_y;
     lp->ext_x = ext_x;
+    static const int env_rows = getenv("GOL_CHUNK_ROWS") ? atoi(getenv("GOL_CHUNK_ROWS")) : 0;  // fixed height (profiling)
+    if (!rows && env_rows > 0) rows = (int)std::min<int64_t>(env_rows, interior);
     if (!rows && !env_warps && k <= 16 && e->tuned_rows[k] > 0) rows = e->tuned_rows[k];
     if (!rows) {
         const int warps_per_sm = env_warps ? env_warps : 12;
@@ -332,7 +336,7 @@ int launch_epoch(gol_engine *e, int k, int in, int out, bool flags, int rec_slot
 // into a free buffer that the next real epoch overwrites - and the fastest is kept.
 int autotune_geometry(gol_engine *e, int k, int in, int scratch)
 {
-    if (k > 16 || e->tuned_rows[k] || e->max_h < 256) return 0;
+    if (k > 16 || e->tuned_rows[k] || e->max_h < 256 || getenv("GOL_CHUNK_ROWS")) return 0;
     const int64_t interior = e->max_h - 2 * GOL_EDGE_ROWS;
     const int min_rows = std::max(8, 2 * k);
     std::vector<int> cands;
@@ -462,13 +466,20 @@ int run_epochs(gol_engine *e, int64_t n, int keep, bool want_flags, bool per_gen
     return 0;
 }
 
+// Flag all-reduce of the record published last + asynchronous read-back of the 8-byte result into
+// pinned host slot `result_index`.  Both run on a second stream behind an event, so the generation
+// stream goes straight on with the next batch (in-stream they cost a ~16 us bubble per batch: a
+// one-CTA kernel, an 8-byte copy and two launch latencies between two epochs).
 int gather_last(gol_engine *e, int result_index)
 {
     const uint32_t rs = e->rec_seq;
     const ArenaLayout &A = e->arena_layout;
+    cudaEvent_t ev = e->ev_flag[result_index & 1];
+    GOL_CUDA(cudaEventRecord(ev, e->stream));
+    GOL_CUDA(cudaStreamWaitEvent(e->flag_stream, ev, 0));
     GOL_TRY(gol_launch_gather(reinterpret_cast<unsigned long long *>(e->arena + A.rec_off),
                               (int)(rs % GOL_REC_SLOTS), e->ndom, rs, e->d_results + result_index, e->d_error,
-                              e->wait_timeout * 4, e->stream));
+                              e->wait_timeout * 4, e->flag_stream));
     ++e->launches;
     return 0;
 }
@@ -548,8 +559,8 @@ int fill_population(gol_engine *e, gol_result *res)
 int post_result(gol_engine *e, int slot)
 {
     GOL_CUDA(cudaMemcpyAsync(&e->h_results[slot], e->d_results + slot, sizeof(unsigned long long), cudaMemcpyDeviceToHost,
-                             e->stream));
-    GOL_CUDA(cudaEventRecord(e->ev_slot[slot & 1], e->stream));
+                             e->flag_stream));
+    GOL_CUDA(cudaEventRecord(e->ev_slot[slot & 1], e->flag_stream));
     return 0;
 }
 
@@ -611,6 +622,7 @@ int run_fast(gol_engine *e, gol_result *res)
                 // replay that batch one generation at a time from its untouched input
                 NvtxRange nv("gol exit replay");
                 GOL_CUDA(cudaStreamSynchronize(e->stream));
+                GOL_CUDA(cudaStreamSynchronize(e->flag_stream));  // the speculative batch's gather: the replay reuses record slots
                 e->cur = pend.ckpt;
                 GOL_TRY(run_epochs(e, pend.n, pend.ckpt, true, true, 1));
                 GOL_TRY(fetch_results(e, pend.n));
@@ -789,6 +801,9 @@ void gol_engine_destroy(gol_engine *e)
         if (ev) cudaEventDestroy(ev);
     for (auto &ev : e->ev_tune)
         if (ev) cudaEventDestroy(ev);
+    for (auto &ev : e->ev_flag)
+        if (ev) cudaEventDestroy(ev);
+    if (e->flag_stream) cudaStreamDestroy(e->flag_stream);
     if (e->own_stream && e->stream) cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -814,6 +829,9 @@ static int engine_create_impl(gol_engine *e)
     GOL_CUDA(cudaEventCreate(&e->ev1));
     GOL_CUDA(cudaEventCreate(&e->ev_tune[0]));
     GOL_CUDA(cudaEventCreate(&e->ev_tune[1]));
+    GOL_CUDA(cudaStreamCreateWithFlags(&e->flag_stream, cudaStreamNonBlocking));
+    GOL_CUDA(cudaEventCreateWithFlags(&e->ev_flag[0], cudaEventDisableTiming));
+    GOL_CUDA(cudaEventCreateWithFlags(&e->ev_flag[1], cudaEventDisableTiming));
     GOL_CUDA(cudaEventCreateWithFlags(&e->ev_slot[0], cudaEventDisableTiming));
     GOL_CUDA(cudaEventCreateWithFlags(&e->ev_slot[1], cudaEventDisableTiming));
 

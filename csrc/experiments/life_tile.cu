@@ -9,8 +9,10 @@
 //
 //   * a CTA of NW warps keeps a tile of 64 words x (NW * R) rows in REGISTERS (R rows x 2 words per
 //     thread) for K generations;
-//   * the tile arrives with one cp.async.bulk.tensor.2d (TMA) into shared memory, completion on an
-//     mbarrier (TMA = 1), or with plain vector loads (TMA = 0);
+//   * the tile arrives through the TMA unit into shared memory, completion on an mbarrier: as
+//     cp.async.bulk.tensor.2d tile loads through a tensor map (TMA = 1) or as one 1-D cp.async.bulk
+//     per tile row (TMA = 2); or with plain vector loads straight into registers (TMA = 0).  The
+//     staged tile starts two words left of the strip so that every row starts on a 16-byte boundary;
 //   * every generation the warps exchange their top / bottom rows through a small shared-memory
 //     buffer; with a cluster of CY CTAs stacked in y the rows at CTA boundaries are read from the
 //     neighbouring CTA's shared memory (DSMEM), so only the outer K rows of the whole cluster
@@ -123,21 +125,32 @@ __device__ __forceinline__ void hsum(const uint32_t (&x)[2], uint32_t (&s0)[2], 
     s0[1] = xor3(l1, x[1], r1); s1[1] = maj3(l1, x[1], r1);
 }
 
+// rows per tensor-map box: the largest divisor of the tile height that is at most 160
+__host__ __device__ constexpr int box_rows(int th)
+{
+    int best = 1;
+    for (int d = 1; d <= 160; ++d)
+        if (th % d == 0) best = d;
+    return best;
+}
+
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
-template <int K, int R, int NW, int CY, bool TMA, int MB>
+template <int K, int R, int NW, int CY, int TMA, int MB>
 __global__ void __launch_bounds__(NW * 32, MB)
 life_tile_kernel(const __grid_constant__ CUtensorMap tmap, const uint32_t *__restrict__ in, uint32_t *__restrict__ out, Grid g)
 {
     constexpr int TH = NW * R;              // rows per CTA
     constexpr int OUT = CY * TH - 2 * K;    // rows a cluster produces
-    constexpr int NBOX = TH <= 256 ? 1 : 2; // a TMA box holds at most 256 rows
-    constexpr int BOXR = TH / NBOX;
+    constexpr int BOXR = box_rows(TH);      // rows per tensor box (<= 256)
+    constexpr int NBOX = TH / BOXR;
     static_assert(BOXR * NBOX == TH && BOXR <= 256, "tile height must split into boxes of <= 256 rows");
+    constexpr int TW = 68;                  // staged words per row: 2 alignment words + the 64 words of the strip (+2)
     extern __shared__ __align__(128) unsigned char smem[];
-    uint32_t *tile = reinterpret_cast<uint32_t *>(smem);                          // [TH][64] (TMA only)
-    uint2 *xch = reinterpret_cast<uint2 *>(smem + (TMA ? TH * 256 : 0));          // [2][NW][2][32]
-    uint64_t *mbar = reinterpret_cast<uint64_t *>(smem + (TMA ? TH * 256 : 0) + 2 * NW * 2 * 32 * 8);
+    uint32_t *tile = reinterpret_cast<uint32_t *>(smem);                          // [TH][TW] (TMA only)
+    constexpr int kTileBytes = TMA ? TH * TW * 4 : 0;
+    uint2 *xch = reinterpret_cast<uint2 *>(smem + kTileBytes);                    // [2][NW][2][32]
+    uint64_t *mbar = reinterpret_cast<uint64_t *>(smem + kTileBytes + 2 * NW * 2 * 32 * 8);
 
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int strip = blockIdx.x;
@@ -148,21 +161,34 @@ life_tile_kernel(const __grid_constant__ CUtensorMap tmap, const uint32_t *__res
 
     uint32_t c[R][2];
     if (TMA) {
+        // rows of the tile that exist in the buffer (the last tiles hang over its end; those rows are never needed)
+        const int nvalid = min(TH, g.rows_padded - (ytop + G));
         if (threadIdx.x == 0) {
             asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(mbar)));
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         }
         __syncthreads();
-        if (threadIdx.x == 0) {
-            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(mbar)), "r"(TH * 256) : "memory");
-            // rows beyond the buffer come back as zeros (out-of-bounds fill)
+        if (TMA == 1) {
+            if (threadIdx.x == 0) {
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(mbar)), "r"(TH * TW * 4) : "memory");
+                // rows beyond the buffer come back as zeros (out-of-bounds fill); x starts on a 16-byte boundary
 #pragma unroll
-            for (int b = 0; b < NBOX; ++b)
-                asm volatile(
-                    "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-                    ::"r"(smem_u32(tile + b * BOXR * 64)), "l"(&tmap), "r"(GOL_GHOST_WORDS32 + lo - kWL), "r"(ytop + G + b * BOXR),
-                    "r"(smem_u32(mbar))
-                    : "memory");
+                for (int b = 0; b < NBOX; ++b)
+                    asm volatile(
+                        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                        ::"r"(smem_u32(tile + b * BOXR * TW)), "l"(&tmap), "r"(GOL_GHOST_WORDS32 + lo - 4), "r"(ytop + G + b * BOXR),
+                        "r"(smem_u32(mbar))
+                        : "memory");
+            }
+        } else if (w == 0) {
+            if (lane == 0)
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(mbar)), "r"(nvalid * TW * 4) : "memory");
+            __syncwarp();
+            const uint32_t *src = in + (int64_t)(ytop + G) * g.pitch + GOL_GHOST_WORDS32 + lo - 4;
+            for (int r = lane; r < nvalid; r += 32)
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                             ::"r"(smem_u32(tile + r * TW)), "l"(src + (int64_t)r * g.pitch), "r"(TW * 4), "r"(smem_u32(mbar))
+                             : "memory");
         }
         uint32_t done = 0;
         while (!done)
@@ -170,7 +196,7 @@ life_tile_kernel(const __grid_constant__ CUtensorMap tmap, const uint32_t *__res
                          : "=r"(done) : "r"(smem_u32(mbar)) : "memory");
 #pragma unroll
         for (int i = 0; i < R; ++i) {
-            const uint2 v = *reinterpret_cast<const uint2 *>(tile + (w * R + i) * 64 + lane * 2);
+            const uint2 v = *reinterpret_cast<const uint2 *>(tile + (w * R + i) * TW + 2 + lane * 2);
             c[i][0] = v.x; c[i][1] = v.y;
         }
     } else {
@@ -253,7 +279,7 @@ static CUtensorMap make_map(const uint32_t *buf, const Grid &g, int box_rows)
     CUtensorMap m;
     const cuuint64_t dims[2] = {(cuuint64_t)g.pitch, (cuuint64_t)g.rows_padded};
     const cuuint64_t strides[1] = {(cuuint64_t)g.pitch * 4};
-    const cuuint32_t box[2] = {64, (cuuint32_t)box_rows};
+    const cuuint32_t box[2] = {68, (cuuint32_t)box_rows};
     const cuuint32_t estr[2] = {1, 1};
     CUresult r = ((EncodeTiled)fn)(&m, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, (void *)buf, dims, strides, box, estr,
                                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -272,13 +298,13 @@ struct Result {
     int ctas;
 };
 
-template <int K, int R, int NW, int CY, bool TMA, int MB>
+template <int K, int R, int NW, int CY, int TMA, int MB>
 static Result run_tile(const char *name, const uint32_t *in, uint32_t *out, const uint32_t *ref, const Grid &g, int reps,
                        unsigned long long *d_diff)
 {
     constexpr int TH = NW * R, OUT = CY * TH - 2 * K;
-    constexpr int BOXR = TH <= 256 ? TH : TH / 2;
-    const size_t smem = (TMA ? (size_t)TH * 256 : 0) + (size_t)2 * NW * 2 * 32 * 8 + 16;
+    constexpr int BOXR = box_rows(TH);
+    const size_t smem = (TMA ? (size_t)TH * 68 * 4 : 0) + (size_t)2 * NW * 2 * 32 * 8 + 16;
     auto kern = life_tile_kernel<K, R, NW, CY, TMA, MB>;
     CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const CUtensorMap map = make_map(in, g, BOXR);
@@ -332,40 +358,53 @@ int main(int argc, char **argv)
     fill_ghosts<<<g.rows_padded, 256>>>(in, g);
     CK(cudaDeviceSynchronize());
 
+    // argv[4]: variant to run (-1 = header line only, 0 = the register pipeline, 1.. = tile variants).
+    // One variant per process, so that a faulting variant cannot take the others with it.
+    const int which = argc > 4 ? atoi(argv[4]) : 0;
+    const int chunk_rows = argc > 5 ? atoi(argv[5]) : 85;
     std::vector<Result> rs;
-    {   // reference: the product's register-pipelined march at its tuned chunk height
-        const int chunk_rows = argc > 4 ? atoi(argv[4]) : 85;
+    {   // reference output (and timing): the product's register-pipelined march at its tuned chunk height
         const int items = ((H + chunk_rows - 1) / chunk_rows) * g.strips;
         march_ref_kernel<K><<<(items + 3) / 4, 128>>>(in, ref, g, chunk_rows);
         CK(cudaDeviceSynchronize());
-        cudaEvent_t e0, e1;
-        CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
-        for (int i = 0; i < 3; ++i) march_ref_kernel<K><<<(items + 3) / 4, 128>>>(in, out, g, chunk_rows);
-        CK(cudaEventRecord(e0));
-        for (int i = 0; i < reps; ++i) march_ref_kernel<K><<<(items + 3) / 4, 128>>>(in, out, g, chunk_rows);
-        CK(cudaEventRecord(e1));
-        CK(cudaEventSynchronize(e1));
-        float ms = 0;
-        CK(cudaEventElapsedTime(&ms, e0, e1));
-        rs.push_back({"register pipeline (product march, no pushes)", ms * 1e3f / reps, 0ull, (items + 3) / 4});
+        if (which == 0) {
+            cudaEvent_t e0, e1;
+            CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+            for (int i = 0; i < 3; ++i) march_ref_kernel<K><<<(items + 3) / 4, 128>>>(in, out, g, chunk_rows);
+            CK(cudaEventRecord(e0));
+            for (int i = 0; i < reps; ++i) march_ref_kernel<K><<<(items + 3) / 4, 128>>>(in, out, g, chunk_rows);
+            CK(cudaEventRecord(e1));
+            CK(cudaEventSynchronize(e1));
+            float ms = 0;
+            CK(cudaEventElapsedTime(&ms, e0, e1));
+            rs.push_back({"register pipeline (product march, no pushes)", ms * 1e3f / reps, 0ull, (items + 3) / 4});
+        }
     }
+    int idx = 0;
 #define TILE(R, NW, CY, TMA, MB) \
+    if (++idx == which)          \
     rs.push_back(run_tile<K, R, NW, CY, TMA, MB>("tile " #R " rows/thread x " #NW " warps, cluster " #CY ", tma " #TMA ", " #MB " CTAs/SM", in, out, ref, g, reps, d_diff))
-    TILE(32, 8, 1, false, 2);
-    TILE(32, 8, 1, true, 2);
-    TILE(34, 8, 1, false, 2);
-    TILE(34, 8, 1, true, 2);
-    TILE(32, 8, 2, true, 2);
-    TILE(34, 8, 2, false, 2);
-    TILE(34, 8, 2, true, 2);
-    TILE(32, 8, 4, true, 2);
-    TILE(34, 8, 4, false, 2);
-    TILE(34, 8, 4, true, 2);
-    TILE(20, 8, 4, true, 3);
-    TILE(20, 8, 1, true, 3);
-    TILE(16, 8, 4, true, 4);
-    printf("# %d x %d, K = %d generations per launch, %d timed launches each\n", W, H, K, reps);
-    printf("# %-52s %10s %12s %8s %s\n", "variant", "us/epoch", "us/generation", "CTAs", "words that differ from the reference");
-    for (const Result &r : rs) printf("  %-52s %10.2f %12.3f %8d %llu\n", r.name, r.us, r.us / K, r.ctas, r.diff);
+    TILE(34, 8, 1, 0, 2);
+    TILE(34, 8, 1, 1, 2);
+    TILE(34, 8, 1, 2, 2);
+    TILE(32, 8, 1, 1, 2);
+    TILE(32, 8, 1, 2, 2);
+    TILE(34, 8, 2, 0, 2);
+    TILE(34, 8, 2, 2, 2);
+    TILE(34, 8, 4, 0, 2);
+    TILE(34, 8, 4, 2, 2);
+    TILE(32, 8, 1, 0, 2);
+    TILE(32, 8, 2, 0, 2);
+    TILE(32, 8, 4, 0, 2);
+    TILE(20, 8, 1, 0, 3);
+    TILE(20, 8, 1, 2, 3);
+    TILE(24, 8, 1, 0, 2);
+    TILE(36, 8, 1, 0, 2);
+    if (which < 0) {
+        printf("# %d x %d, K = %d generations per launch, %d timed launches each, %d tile variants\n", W, H, K, reps, idx);
+        printf("# %-58s %10s %14s %7s %s\n", "variant", "us/epoch", "us/generation", "CTAs", "words that differ from the reference");
+    }
+    for (const Result &r : rs) printf("  %-58s %10.2f %14.3f %7d %llu\n", r.name, r.us, r.us / K, r.ctas, r.diff);
+    fflush(stdout);
     return 0;
 }

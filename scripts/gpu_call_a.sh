@@ -3,7 +3,7 @@
 # per-launch trace of run().  Every step under its own timeout.
 OUT=gpurun_out; mkdir -p $OUT
 echo "== pytest"; timeout 420 python -m pytest tests -m gpu -q --timeout 150 2>&1 | tail -25 > $OUT/pytest_gpu.log; cat $OUT/pytest_gpu.log
-echo "== tilebench"; timeout 90 bin/gol-tilebench 16384 16384 20 > $OUT/tilebench_16384.txt 2>&1; cat $OUT/tilebench_16384.txt
+echo "== tilebench"; timeout 300 scripts/tilebench.sh 16384 16384 20 > $OUT/tilebench_16384.txt 2>&1; cat $OUT/tilebench_16384.txt
 echo "== cli"
 timeout 300 python - > $OUT/cli_phases.txt 2>&1 <<'PY'
 import os, subprocess, tempfile, time

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Exercises the non-stencil kernels at a profiling-friendly size (8192 x 8192): text parse / format,
-cell pack / unpack, generator, population, generic step, first halo exchange, alive scan + gather."""
+cell pack / unpack, generator, population, checksum, generic step, first halo exchange, alive scan + gather."""
 import os
 import sys
 import tempfile
@@ -27,4 +27,5 @@ life.load_packed(g)
 life.save(path)
 life.load_file(path)
 print(life.run())
+print("checksum", hex(life.local_hash()), "population", life.population())
 life.close()
