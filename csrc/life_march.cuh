@@ -117,6 +117,10 @@ struct GlobalRowSource {
     }
 };
 
+#ifndef GOL_WARM_SPLIT
+#define GOL_WARM_SPLIT 1   // prune the inactive levels of the pipeline fill (see march)
+#endif
+
 // One warp streams rows [y0-K, y1+K) of generation g through K register-resident levels and
 // writes rows [y0, y1) of generation g+K.  FAST: every lane does a plain vector load and a
 // (predicated) vector store - true for all strips except the ragged right edge of a row.
@@ -176,66 +180,61 @@ __device__ __forceinline__ void march(const MarchArgs &A, Source &src, uint32_t 
         }
     };
 
-    // Three kinds of step.  FILL steps are the pipeline fill: level t only starts once its first
-    // valid input row (y0-K+t) has come down the chain, i.e. at step r = rbeg + 2t.  The levels of a
-    // step form a chain, so the inactive ones are a suffix and a fill step simply stops early; nothing
-    // is emitted yet.  This removes K(K-1) of the 2K*K fill/drain level-steps of a chunk.  The two
-    // PRIME steps after the fill run all K levels but their last-level rows (y0-2, y0-1) lie above
-    // the chunk: nothing is stored and nothing enters the flags.  Every MAIN step emits a row, so the
-    // steady-state loop carries no "is this row mine" test at all.
-    constexpr int FILL = 0, PRIME = 1, MAIN = 2;
-    auto step = [&](int r, auto par_tag, auto kind_tag) {
-        constexpr int KIND = decltype(kind_tag)::value;
+    // WARM steps are the pipeline fill: level t only starts once its first valid input row
+    // (y0-K+t) has come down the chain, i.e. at step r = rbeg + 2t.  The levels of a step form a
+    // chain, so the inactive ones are a suffix and a warm step simply stops early; nothing is
+    // emitted yet.  This removes K(K-1) of the 2K*K fill level-steps of a chunk.
+    auto step = [&](int r, auto par_tag, auto warm_tag) {
+        constexpr bool WARM = decltype(warm_tag)::value;
         uint32_t x0[kWL], fin[kWL];
 #pragma unroll
         for (int j = 0; j < kWL; ++j) { x0[j] = q[decltype(par_tag)::value][j]; fin[j] = 0; }
         if (r + 2 < rload_end) src.template load<FAST>(A, q[decltype(par_tag)::value]);
+        const bool emit = !WARM && r - K >= A.y0;
         auto run = [&](auto self, auto t_tag, const uint32_t(&x)[kWL]) -> void {
             constexpr int t = decltype(t_tag)::value;
             uint32_t o[kWL];
-            level(t_tag, par_tag, x, o, KIND == MAIN);
+            level(t_tag, par_tag, x, o, emit);
             if constexpr (t == K - 1) {
 #pragma unroll
                 for (int j = 0; j < kWL; ++j) fin[j] = o[j];
             } else {
-                if (KIND != FILL || r >= rbeg + 2 * (t + 1)) self(self, std::integral_constant<int, t + 1>{}, o);
+                if (!WARM || r >= rbeg + 2 * (t + 1)) self(self, std::integral_constant<int, t + 1>{}, o);
             }
         };
         run(run, std::integral_constant<int, 0>{}, x0);
-        if constexpr (KIND == MAIN) {  // fin = row (r - K) of generation g+K
-            if (FAST) {
-                if (store_all) stg_v2(pout, fin[0], fin[1]);
-            } else if (store_any) {
-                if (store_all) {
-                    stg_v2(pout, fin[0], fin[1]);
-                } else {
+        if constexpr (!WARM) {
+            if (emit) {  // fin = row (r - K) of generation g+K
+                if (FAST) {
+                    if (store_all) stg_v2(pout, fin[0], fin[1]);
+                } else if (store_any) {
+                    if (store_all) {
+                        stg_v2(pout, fin[0], fin[1]);
+                    } else {
 #pragma unroll
-                    for (int j = 0; j < kWL; ++j)
-                        if (A.keep[j]) stg_u32(pout + j, fin[j] & A.keep[j]);
+                        for (int j = 0; j < kWL; ++j)
+                            if (A.keep[j]) stg_u32(pout + j, fin[j] & A.keep[j]);
+                    }
                 }
+                pout += pitch;
             }
-            pout += pitch;
         }
     };
-    using P0 = std::integral_constant<int, 0>;
-    using P1 = std::integral_constant<int, 1>;
 
     int r = rbeg;
-    // fill: 2K-2 steps (always even, so the window parity stays aligned)
+#if GOL_WARM_SPLIT
+    // fill: 2K-2 steps (always even, so the window parity stays aligned); chunks are >= 1 row, so
+    // the loop below still has at least 3 steps left
     for (; r < rbeg + 2 * K - 2; r += 2) {
-        step(r, P0{}, std::integral_constant<int, FILL>{});
-        step(r + 1, P1{}, std::integral_constant<int, FILL>{});
+        step(r, std::integral_constant<int, 0>{}, std::true_type{});
+        step(r + 1, std::integral_constant<int, 1>{}, std::true_type{});
     }
-    // r = y0 + K - 2: the two steps whose output rows are y0-2 and y0-1
-    step(r, P0{}, std::integral_constant<int, PRIME>{});
-    step(r + 1, P1{}, std::integral_constant<int, PRIME>{});
-    r += 2;
-    // r = y0 + K: every remaining step emits row r - K; chunks are >= 1 row, so at least one step is left
+#endif
     for (; r + 1 < rend; r += 2) {
-        step(r, P0{}, std::integral_constant<int, MAIN>{});
-        step(r + 1, P1{}, std::integral_constant<int, MAIN>{});
+        step(r, std::integral_constant<int, 0>{}, std::false_type{});
+        step(r + 1, std::integral_constant<int, 1>{}, std::false_type{});
     }
-    if (r < rend) step(r, P0{}, std::integral_constant<int, MAIN>{});
+    if (r < rend) step(r, std::integral_constant<int, 0>{}, std::false_type{});
 
     if (FLAGS) {
         flag_alive = (acc_a[0] & A.keep[0]) | (acc_a[1] & A.keep[1]);
