@@ -52,6 +52,7 @@ struct Shared {  // rendezvous area shared by the forked ranks
 };
 
 bool g_is_parent = false;   // the process that forked the other ranks (rank 0)
+double g_start_ms = 0;      // steady-clock time at the start of main (phase report of --stats)
 
 // Has a forked rank died without reporting (signal, abort, non-zero exit)?  Only the parent can
 // see that; WNOWAIT leaves the child for the final waitpid in main().
@@ -198,6 +199,7 @@ int run_rank(const Options &opt, int rank, int nproc, Shared *sh)
     cfg.start_generation = opt.start_gen;
     cfg.flags = opt.generic ? GOL_FLAG_FORCE_GENERIC : 0;
     gol_engine *eng = nullptr;
+    const double t_create0 = now_ms();
     if (gol_engine_create(&cfg, &eng)) {
         // a decomposition finer than the strip kernel's minimum domain: fall back to one domain
         // (only possible when all domains live in this process)
@@ -223,6 +225,7 @@ int run_rank(const Options &opt, int rank, int nproc, Shared *sh)
         barrier(sh, nproc);
     }
 
+    const double create_ms = now_ms() - t_create0;
     double t0 = now_ms();
     if (opt.have_random) {
         if (gol_engine_randomize(eng, opt.seed)) die(sh, "randomize");
@@ -238,7 +241,10 @@ int run_rank(const Options &opt, int rank, int nproc, Shared *sh)
         printf("Reading file:\t%.2lf msecs\n", ms);
     }
 
+    const double t_prep0 = now_ms();
     if (gol_engine_prepare(eng)) die(sh, "prepare");
+    gol_engine_sync(eng);
+    const double prepare_ms = now_ms() - t_prep0;
     gol_result res;
     if (gol_engine_run(eng, &res)) die(sh, "run");
     sh->loop_ms[rank] = res.loop_ms;
@@ -274,12 +280,14 @@ int run_rank(const Options &opt, int rank, int nproc, Shared *sh)
             const double cells = (double)opt.width * (double)opt.height;
             fprintf(stderr,
                     "[gol] exit=%s generations=%d computed=%lld loop_ms=%.3f cell_updates_per_s=%.4g population=%llu "
-                    "fast_path=%d launches=%lld grid=%dx%d chunk_rows=%d deep_halo=%d\n",
+                    "fast_path=%d launches=%lld grid=%dx%d chunk_rows=%d deep_halo=%d | phases [ms]: since_start=%.0f create=%.0f "
+                    "read=%.0f prepare=%.0f loop=%.1f write=%.0f\n",
                     res.exit_reason == GOL_EXIT_EMPTY ? "empty" : res.exit_reason == GOL_EXIT_SIMILAR ? "similar" : "limit",
                     res.generations, (long long)res.generations_computed, loop_ms,
                     cells * (double)res.generations_computed / (loop_ms * 1e-3), pop, gol_engine_uses_fast_path(eng),
                     (long long)gol_engine_launch_count(eng), cfg.grid_rows, cfg.grid_cols, gol_engine_chunk_rows(eng),
-                    gol_engine_uses_deep_halo(eng));
+                    gol_engine_uses_deep_halo(eng), now_ms() - g_start_ms, create_ms, sh->read_ms[0], prepare_ms, loop_ms,
+                    sh->write_ms[0]);
         }
         if (opt.show && nproc == 1) {
             // the reference's show() (S:42-58, dead code there): VT100 reverse-video blocks on stdout
@@ -309,6 +317,7 @@ int run_rank(const Options &opt, int rank, int nproc, Shared *sh)
 
 int main(int argc, char **argv)
 {
+    g_start_ms = now_ms();
     Options opt;
     if (const char *v = getenv("GOL_VARIANT")) opt.variant = v;
     if (const char *v = getenv("GOL_GEN_LIMIT")) opt.gen_limit = atoi(v);
@@ -403,7 +412,8 @@ int main(int argc, char **argv)
                 if (pid == 0) {
                     g_is_parent = false;
                     run_rank(opt, r, nproc, sh);
-                    if (mpi_like && opt.variant != "openmp") { printf("Finished\n"); fflush(stdout); }
+                    if (mpi_like && opt.variant != "openmp") printf("Finished\n");
+                    fflush(nullptr);
                     _exit(0);
                 }
                 kids.push_back(pid);

@@ -820,8 +820,10 @@ static int engine_create_impl(gol_engine *e)
         GOL_FAIL("CUDA device %d requested but %d device(s) are visible (one process per GPU: the process count "
                  "must not exceed the GPU count)", cfg.device, ndev);
     GOL_CUDA(cudaSetDevice(cfg.device));
-    cudaDeviceProp prop;
-    GOL_CUDA(cudaGetDeviceProperties(&prop, cfg.device));
+    // two attributes instead of cudaGetDeviceProperties (which queries everything and is slow at start-up)
+    struct { int multiProcessorCount = 148, clockRate = 1965000; } prop;
+    GOL_CUDA(cudaDeviceGetAttribute(&prop.multiProcessorCount, cudaDevAttrMultiProcessorCount, cfg.device));
+    GOL_CUDA(cudaDeviceGetAttribute(&prop.clockRate, cudaDevAttrClockRate, cfg.device));   // kHz
     e->num_sms = prop.multiProcessorCount;
     GOL_CUDA(cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking));
     e->own_stream = true;

@@ -7,8 +7,6 @@
 # against the round-1 engine interface and are no longer built.
 set -e
 cd "$(dirname "$0")/.."
-mkdir -p bin
-ARCH="-gencode arch=compute_100a,code=sm_100a"
-nvcc $ARCH -O3 -std=c++17 -lineinfo -Xptxas -v -Iinclude csrc/experiments/life_tile.cu -o bin/gol-tilebench 2> build/life_tile.ptxas.log || { cat build/life_tile.ptxas.log; exit 1; }
+make bin/gol-tilebench
 grep -E "life_tile_kernel|registers|spill" build/life_tile.ptxas.log | grep -A1 "life_tile_kernel" | grep -E "registers" | sort | uniq -c
 ls -la bin/gol-tilebench
