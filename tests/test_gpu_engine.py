@@ -158,6 +158,13 @@ def test_generic_path_small_grids(cuda_device):
         assert r is not None
     life = make(30, 30)
     assert not life.uses_fast_path
+    from gol_b200.ops import cpu
+    g30 = cpu.random_grid(30, 30, 8)
+    life.load_packed(g30)
+    assert life.local_hash() == cpu.grid_hash(g30, 30) and life.population() == int(cpu.unpack(g30, 30).sum())
+    blocks = [torch.empty(life.local_block_shape(0), dtype=torch.int64).pin_memory()]
+    life.download_local(blocks)
+    assert np.array_equal(blocks[0].numpy().view(np.uint64), g30)
     life.close()
     run_both(patterns.grid_with(30, 30, ("block", 3, 3)))
     run_both(patterns.grid_with(512, 64, ("block", 3, 3)), force_generic=True)
@@ -309,6 +316,32 @@ def test_deep_halo_pairs_emulated(cuda_device, monkeypatch, grid):
     from gol_b200.utils import patterns
     cells = patterns.grid_with(1024, 128, ("tromino", 510, 62), ("diag3", 700, 100))
     run_both(cells, gen_limit=200, grid=grid if 128 // grid[0] >= 16 else (1, 1))
+
+
+def test_per_domain_stage_download_and_checksum(cuda_device):
+    # a rank that keeps only its own blocks on the host: stage_local / download_local per local domain,
+    # and the decomposition-independent checksum (sum over domains == host checksum of the global grid)
+    from gol_b200.ops import cpu
+    w, h = 2240, 384
+    start = cpu.random_grid(w, h, 6)
+    for grid in [(1, 1), (2, 2), (4, 1), (1, 3)]:
+        life = make(w, h, grid=grid, gen_limit=24)
+        ins, outs = [], []
+        for i, g in enumerate(life.local_domains):
+            x0, y0, dw, dh = life.domain_extent(g)
+            blk = np.ascontiguousarray(start[y0:y0 + dh, x0 // 64:(x0 + dw + 63) // 64]).view(np.int64)
+            ins.append(torch.from_numpy(blk).pin_memory())
+            outs.append(torch.empty(life.local_block_shape(i), dtype=torch.int64).pin_memory())
+        life.stage_local(ins).commit_staged()
+        assert life.local_hash() == cpu.grid_hash(start, w)
+        res = life.run()
+        want, wres = cpu.run(start, w, gen_limit=24)
+        assert res.generations == wres.generations and life.local_hash() == cpu.grid_hash(want, w)
+        life.download_local(outs)
+        for i, g in enumerate(life.local_domains):
+            x0, y0, dw, dh = life.domain_extent(g)
+            assert np.array_equal(outs[i].numpy().view(np.uint64), want[y0:y0 + dh, x0 // 64:(x0 + dw + 63) // 64]), (grid, g)
+        life.close()
 
 
 def test_staged_upload(cuda_device):
