@@ -23,5 +23,6 @@ r, c = (int(v) for v in a.grid.split("x"))
 life = gol_b200.GameOfLife(a.size, a.size, grid=(r, c), device=0, gen_limit=a.gens)
 life.randomize(1)
 res = life.run()
-print(f"run: {res.generations} generations of {a.size}^2 in {res.loop_ms:.3f} ms, chunk_rows {life.chunk_rows}", flush=True)
+print(f"run: {res.generations} generations of {a.size}^2 in {res.loop_ms:.3f} ms, chunk_rows {life.chunk_rows}, "
+      f"checksum {life.local_hash():016x}, population {life.population()}", flush=True)
 life.close()
