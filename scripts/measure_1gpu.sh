@@ -1,5 +1,5 @@
 #!/bin/bash
-# One-GPU measurement pass: GPU test suite, tile-kernel experiment, CLI phase times, early-exit cost,
+# One-GPU measurement pass (scripts/measure_1gpu.sh): GPU test suite, tile-kernel experiment, CLI phase times, early-exit cost,
 # per-launch trace of run().  Every step under its own timeout.
 OUT=gpurun_out; mkdir -p $OUT
 echo "== pytest"; timeout 420 python -m pytest tests -m gpu -q --timeout 150 2>&1 | tail -25 > $OUT/pytest_gpu.log; cat $OUT/pytest_gpu.log
