@@ -18,7 +18,7 @@ LIB       := libgolb200.so
 CU_SRCS   := csrc/life_kernels.cu csrc/dense_kernels.cu csrc/engine.cu csrc/static_scratch.cu
 CPP_SRCS  := csrc/host_util.cpp
 OBJS      := $(CU_SRCS:csrc/%.cu=$(BUILD)/%.o) $(CPP_SRCS:csrc/%.cpp=$(BUILD)/%.o)
-HDRS      := include/gol_b200.h csrc/gol_internal.h csrc/life_rule.h csrc/life_march.cuh
+HDRS      := include/gol_b200.h csrc/gol_internal.h csrc/life_rule.h csrc/life_march.cuh csrc/life_items.h
 
 all: $(LIB) bin/gol bin/gol-generate bin/gol-intpeak bin/gol-tilebench
 

@@ -22,22 +22,13 @@
 
 #include "gol_internal.h"
 #include "life_march.cuh"
+#include "life_items.h"
 
 namespace {
 
 using namespace golk;
 
 constexpr int kWarps = GOL_STRIP_WARPS;  // warps per CTA
-
-// Strips are kVW owned words wide.  A launch may also compute `xe` ghost words on each side of
-// the row (deep-halo pairs), i.e. the words [-xe, nw + xe).  The last strip is right-aligned to
-// the end of that range (it may overlap its left neighbour, which then computes identical words
-// twice) so that it always owns the row's last 128 cells, which it pushes east.
-__host__ __device__ __forceinline__ int strip_count(int nw, int xe) { return (nw + 2 * xe + kVW - 1) / kVW; }
-__device__ __forceinline__ int strip_origin(int strip, int S, int nw, int xe)
-{
-    return (strip == S - 1 && S > 1) ? nw + xe - kVW : strip * kVW - xe;
-}
 
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p)
 {
@@ -216,78 +207,6 @@ __device__ bool wait_neighbors(const GolDomainDev &D, uint32_t want, uint32_t di
     return ok;
 }
 
-// Work items of a domain are (strip, chunk) pairs.  The computed row range [ylo, yhi) is cut into
-// a short first and last chunk of `edge_rows` rows - exactly the rows that are pushed to the north
-// and south neighbours, so those items finish (and their flags leave) long before the tall
-// interior chunks of the same launch - and interior chunks of `chunk_rows` rows.  Domains shorter
-// than three edge chunks are a single chunk.  Items are numbered so that everything that touches
-// a ghost zone comes first: the two edge chunks, then the first/last strip of the interior
-// chunks, then the interior (or in the reverse order: border_last).
-struct ItemMap {
-    int S, ylo, yhi, E, rows, ci, nedge;
-    int nA, nB, e, n_items;
-};
-__device__ __forceinline__ ItemMap item_map(const GolDomainDev &D, const GolLaunch &lp)
-{
-    ItemMap m;
-    m.S = strip_count(D.nw32, lp.ext_x);
-    m.ylo = -lp.ext_y;
-    m.yhi = D.H + lp.ext_y;
-    m.rows = lp.chunk_rows;
-    const int span = m.yhi - m.ylo;
-    if (lp.edge_rows <= 0 || span < 3 * lp.edge_rows) {
-        m.E = span; m.nedge = 1; m.ci = 0;
-    } else {
-        m.E = lp.edge_rows; m.nedge = 2;
-        m.ci = (span - 2 * m.E + m.rows - 1) / m.rows;
-    }
-    m.e = min(m.S, 2);
-    m.nA = m.nedge * m.S;
-    m.nB = m.ci * m.e;
-    m.n_items = m.nA + m.nB + m.ci * (m.S - m.e);
-    return m;
-}
-struct Item {
-    int strip, y0, y1;
-    bool top, bot, first, last;   // chunk reads the north / south ghost rows; strip reads the west / east ghost slot
-};
-// returns false for idle items (beyond this domain's item count)
-__device__ __forceinline__ bool decode_item(const ItemMap &m, int item, bool border_last, Item &it)
-{
-    if (item >= m.n_items) return false;
-    if (border_last) item = m.n_items - 1 - item;
-    int chunk;  // 0 = first edge chunk, 1..ci = interior, ci+1 = last edge chunk
-    if (item < m.nA) {
-        const int which = item / m.S;
-        it.strip = item - which * m.S;
-        chunk = which == 0 ? 0 : m.ci + 1;
-    } else if (item < m.nA + m.nB) {
-        item -= m.nA;
-        const int c = item / m.e;
-        it.strip = (item - c * m.e) ? m.S - 1 : 0;
-        chunk = 1 + c;
-    } else {
-        item -= m.nA + m.nB;
-        const int c = item / (m.S - 2);
-        it.strip = 1 + item - c * (m.S - 2);
-        chunk = 1 + c;
-    }
-    if (chunk == 0) { it.y0 = m.ylo; it.y1 = m.ylo + m.E; }
-    else if (chunk == m.ci + 1) { it.y0 = m.yhi - m.E; it.y1 = m.yhi; }
-    else { it.y0 = m.ylo + m.E + (chunk - 1) * m.rows; it.y1 = min(m.yhi - m.E, it.y0 + m.rows); }
-    it.top = chunk == 0;
-    it.bot = m.nedge == 1 || chunk == m.ci + 1;
-    it.first = it.strip == 0;
-    it.last = it.strip == m.S - 1;
-    return true;
-}
-__device__ __forceinline__ uint32_t item_dir_mask(const Item &it)
-{
-    return (it.top ? 1u : 0u) | (it.bot ? 2u : 0u) | (it.first ? 4u : 0u) | (it.last ? 8u : 0u) |
-           (it.top && it.first ? 16u : 0u) | (it.top && it.last ? 32u : 0u) | (it.bot && it.first ? 64u : 0u) |
-           (it.bot && it.last ? 128u : 0u);
-}
-
 // Called by every border warp after its pushes.  Two direction groups are counted separately:
 // the edge-chunk items carry everything that goes N / S and to the corners, the first/last-strip
 // items everything that goes W / E; the warp that completes a group publishes that group's flags.
@@ -411,7 +330,7 @@ life_strip_kernel(const GolDomainDev *__restrict__ doms, const GolLaunch lp)
     const GolDomainDev &D = doms[dom_id];
     const int lane = threadIdx.x & 31;
     const int item = cta * kWarps + (threadIdx.x >> 5);
-    const ItemMap im = item_map(D, lp);
+    const ItemMap im = item_map(D.nw32, D.H, lp);
     Item it;
     // Everything above reads only the launch parameters and the domain descriptor (constant after
     // upload).  Let the next launch become resident, then wait for the previous one to complete
@@ -437,7 +356,7 @@ __global__ void __launch_bounds__(kWarps * 32) halo_push_kernel(const GolDomainD
     const GolDomainDev &D = doms[dom_id];
     const int lane = threadIdx.x & 31;
     const int item = cta * kWarps + (threadIdx.x >> 5);
-    const ItemMap im = item_map(D, lp);
+    const ItemMap im = item_map(D.nw32, D.H, lp);
     Item it;
     if (!decode_item(im, item, false, it) || !(it.top || it.bot || it.first || it.last)) return;
     push_borders(D, lp.out_idx, it.strip, im.S, it.y0, it.y1, lp.push_rows, lane);
@@ -454,7 +373,7 @@ __global__ void __launch_bounds__(kWarps * 32) scan_alive_kernel(const GolDomain
     const GolDomainDev &D = doms[dom_id];
     const int lane = threadIdx.x & 31;
     const int item = cta * kWarps + (threadIdx.x >> 5);
-    const ItemMap im = item_map(D, lp);
+    const ItemMap im = item_map(D.nw32, D.H, lp);
     Item it;
     if (decode_item(im, item, false, it)) {
         const int lo = strip_origin(it.strip, im.S, D.nw32, 0), hi = min(D.nw32, lo + kVW);
